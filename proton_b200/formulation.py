@@ -1,0 +1,204 @@
+"""Per-line FDM formulation: the in-memory twin of PROTON's `Matrix_Formulation_Class`.
+
+The reference (matrix_formulation_func_cli.py:24-299) builds dense N x N / N x S Python lists and
+writes `B.csv`, `curden.csv` and `analytical.txt` for the C++ kernel.  This module produces the same
+numbers — N, `Acoef`, the non-zero triplets of `B` in the order the reference writes them, and the
+float32-rounded current densities — without the O(N^2) dense build and without touching disk, so a
+whole power grid can be handed to the batched GPU path.  `read_line_inputs` reads the files the
+reference emitted instead, for callers that already ran it.
+
+Reference quirks reproduced on purpose (each one changes the numbers the kernel sees):
+  * constants exactly as written, incl. `b = Ea*Z*rho/Omega`            (:48-73)
+  * points mode: dx = round(total/(points + S - 1), 2) um               (:86-102)
+  * nodes per segment = round(len/dx) with Python's banker's rounding   (:133)
+  * a segment is joined to its predecessor (shares a via node) only when the coordinate that is
+    constant along the CURRENT segment equals the predecessor's                (:148-157)
+  * `B` is assigned, not accumulated: later assignments overwrite earlier ones, row index -1
+    wraps to the last row (Python list indexing), and the closing assignment
+    B[N-1][S-1] = -1 overwrites whatever was there (e.g. the N == 1 case)      (:191-204)
+  * current density is rounded to float32 (`array.array('f')`)                 (:121,180)
+"""
+from __future__ import annotations
+
+import math
+import os
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+NOT_DENSE_MSG = "The given discretization is not dense enough for the geometry of the given line."
+NO_METHOD_MSG = "Error no discretization method is choosen!"
+CORRUPT_MSG = "Corrupted CSV segments file."
+NOT_FOUND_MSG = "CSV file not found."
+
+
+class FormulationError(ValueError):
+    """Raised with the same message text the reference returns/prints for this condition."""
+
+
+@dataclass
+class LineInputs:
+    """What the analytical kernel consumes for one line."""
+    name: str
+    num_nodes: int            # nx_total  -> analytical.cfg num_nodes
+    a_coeff: float            # Acoef     -> analytical.cfg A_coeff
+    rows: np.ndarray          # B.csv triplets, int32, in file order (row-major over the dense B)
+    cols: np.ndarray
+    vals: np.ndarray          # float64 (= +-bcoef)
+    curden: np.ndarray        # float64 holding float32-rounded values, length S
+    dx: float = 0.0
+    bcoef: float = 0.0
+
+
+def technology_constants(technology: str, temperature: float) -> Tuple[float, float]:
+    """(kappa, b) for 'CuDD' or anything else (= the reference's Al branch), :48-73."""
+    T = float(temperature)
+    if technology == "CuDD":
+        D0, Ea, kB, B0, Omega, rho, Z = 1.3e-9, 1.609e-19, 1.3806e-23, 28e9, 1.182e-29, 2.25e-8, 1
+    else:
+        D0, Ea, kB, B0, Omega, rho, Z = 1e-4, 1.92e-29, 1.3806e-23, 80e9, 2e-29, 3.16e-8, 1
+    Da = D0 * math.exp(-Ea / (kB * T))
+    kappa = (Da * B0 * Omega) / (kB * T)
+    b = Ea * Z * rho / Omega
+    return kappa, b
+
+
+def parse_line_csv(csv_file: str) -> Tuple[List[Tuple[str, str, float, float]], int]:
+    """Rows of a `<layer>_<net>_<k>.csv` (spice_function_cli.py:263,275) that start with 'R':
+    (left_node, right_node, length_um, current_A).  Node names keep the leading blank the reference's
+    `split(',')` leaves in place.  Also returns the raw line count (used by points mode)."""
+    try:
+        with open(csv_file) as f:
+            lines = f.readlines()
+    except FileNotFoundError:
+        raise FormulationError(NOT_FOUND_MSG)
+    segs = []
+    try:
+        for line in lines:
+            if line and line[0] == "R":
+                c = line.split(",")
+                segs.append((c[1], c[2], float(c[3]), float(c[4])))
+    except (ValueError, IndexError):
+        raise FormulationError(CORRUPT_MSG)
+    return segs, len(lines)
+
+
+def formulate_segments(segs: Sequence[Tuple[str, str, float, float]], *, sp_step=None, given_disc_point=None,
+                       technology="CuDD", temperature=378.0, givenWidth=0.1, name="line",
+                       n_file_lines: Optional[int] = None) -> LineInputs:
+    """Discretise one line given its segments (left_node, right_node, length_um, current_A)."""
+    if sp_step is None and given_disc_point is None:
+        raise FormulationError(NO_METHOD_MSG)
+    kappa, b = technology_constants(technology, temperature)
+    S_all = len(segs)
+    dx = 0.0
+    if given_disc_point is not None:
+        total_length = 0.0
+        for s in segs:
+            total_length = total_length + float(s[2])
+        nl = (S_all + 1) if n_file_lines is None else n_file_lines
+        gdp = float(given_disc_point) + (nl - 2)
+        dx = round(float(total_length / gdp), 2)
+        dx = dx * 1e-6
+    w = float(givenWidth)
+    nx_total = 0
+    num_segments = 0
+    curden_list = []
+    vias_nodes: List[int] = []
+    vias = {}
+    left_node = right_node = None
+    for (ln, rn, length_um, current) in segs:
+        num_segments += 1
+        length = float(length_um) * 1e-6
+        curden_list.append(float(current) / (w * 1e-6 * w * 1e-6))
+        if sp_step is not None:
+            dx = float(sp_step) * 1e-6
+        if length < dx:
+            raise FormulationError(NOT_DENSE_MSG)
+        disc_points = round(length / dx)
+        nx_total += disc_points
+        prev_left, prev_right = left_node, right_node
+        left_node, right_node = ln, rn
+        lc, rc = left_node.split("_"), right_node.split("_")
+        same = 2 if lc[2] == rc[2] else 1
+        if prev_left and prev_right and prev_left.split("_")[same] == lc[same]:
+            key = nx_total - disc_points
+            vias[key] = num_segments
+            vias_nodes.append(key)
+            nx_total -= 1
+    N, S = nx_total, num_segments
+    if N <= 0 or S <= 0:
+        raise FormulationError(CORRUPT_MSG)
+    entries = {}
+
+    def assign(i: int, j: int, v: float) -> None:
+        if i < 0:
+            i += N
+        if j < 0:
+            j += S
+        if not (0 <= i < N and 0 <= j < S):
+            raise IndexError("list assignment index out of range")
+        entries[(i, j)] = v
+
+    assign(0, 0, 1.0)
+    for node in vias_nodes:
+        segment = vias[node]
+        assign(node - 1, segment - 2, -1.0)
+        assign(node - 1, segment - 1, 1.0)
+    assign(N - 1, S - 1, -1.0)
+    acoef = kappa / (dx * dx)
+    bcoef = kappa * b / dx
+    keys = sorted(entries)
+    rows = np.array([k[0] for k in keys], dtype=np.int32)
+    cols = np.array([k[1] for k in keys], dtype=np.int32)
+    vals = np.array([entries[k] * bcoef for k in keys], dtype=np.float64)
+    curden = np.asarray(curden_list, dtype=np.float64).astype(np.float32).astype(np.float64)
+    return LineInputs(name=name, num_nodes=int(N), a_coeff=float(acoef), rows=rows, cols=cols, vals=vals,
+                      curden=curden, dx=float(dx), bcoef=float(bcoef))
+
+
+def formulate_csv(csv_file: str, *, sp_step=None, given_disc_point=None, technology="CuDD", temperature=378.0,
+                  givenWidth=0.1) -> LineInputs:
+    """`Matrix_Formulation_Class(csv_file, ..).matrix_formulation()` without the files."""
+    segs, nlines = parse_line_csv(csv_file)
+    name = os.path.splitext(os.path.basename(csv_file))[0]
+    return formulate_segments(segs, sp_step=sp_step, given_disc_point=given_disc_point, technology=technology,
+                              temperature=temperature, givenWidth=givenWidth, name=name, n_file_lines=nlines)
+
+
+def analyze_policy_step(segs: Sequence[Tuple[str, str, float, float]]) -> float:
+    """The whole-grid driver's choice of step: 0.99 x the shortest segment (PROTON_cli.py:1005-1012)."""
+    return float(min(float(s[2]) for s in segs) * 0.99)
+
+
+def read_line_inputs(input_dir: str, name: Optional[str] = None) -> LineInputs:
+    """Read what the reference's formulation wrote for one line: `analytical.txt`
+    (analytical_class_cli.py:31-41), `B.csv` (int,int,double triplets; separators ',', blank, tab as in
+    tripletParser, bin/EMtool_analytical@0xb010) and `curden.csv` (one double per line, @0xba39)."""
+    nx_total, acoef = None, None
+    with open(os.path.join(input_dir, "analytical.txt")) as f:
+        for line in f:
+            words = line.split()
+            if "Acoef" in words:
+                acoef = float(words[2])
+            if "nx_total" in words:
+                nx_total = int(words[2])
+    if nx_total is None or acoef is None:
+        raise FormulationError(f"analytical.txt in {input_dir} lacks nx_total/Acoef")
+    rows, cols, vals = [], [], []
+    with open(os.path.join(input_dir, "B.csv")) as f:
+        for k, line in enumerate(f, start=1):
+            tok = line.replace(",", " ").split()
+            if not tok:
+                continue
+            if len(tok) < 2:
+                raise FormulationError(f"Required second value at line {k} of the file B.csv")
+            if len(tok) < 3:
+                raise FormulationError(f"Required third value at line {k} of the file B.csv")
+            rows.append(int(tok[0])), cols.append(int(tok[1])), vals.append(float(tok[2]))
+    with open(os.path.join(input_dir, "curden.csv")) as f:
+        curden = [float(x) for x in f.read().split()]
+    return LineInputs(name=name or os.path.basename(os.path.normpath(input_dir)), num_nodes=nx_total,
+                      a_coeff=acoef, rows=np.asarray(rows, np.int32), cols=np.asarray(cols, np.int32),
+                      vals=np.asarray(vals, np.float64), curden=np.asarray(curden, np.float64))
