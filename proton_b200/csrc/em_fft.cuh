@@ -1,0 +1,444 @@
+// em_fft.cuh — fused modal evaluation + inverse DCT (DCT-III) + stress write-back + per-line max.
+//
+// Replaces calc_analytical_solution + idct1d of the reference (bin/EMtool_analytical@0xc68c, @0xc2a0;
+// SURVEY.md §8a rows 10-12) for every timestamp of a line in one kernel.
+//
+// Math.  For one line with N nodes the reference computes, per timestamp t,
+//     sigma_n = sum_k Y_k cos(pi k (2n+1) / (2N)),   Y_k = D_k(t) * (forward-DCT weight of mode k).
+// Two timestamps (t1, t2) are packed into ONE length-N complex inverse DFT (Makhoul's permutation):
+//     U_0 = Y1_0 + i Y2_0,   U_k = e^{i pi k/2N} [ (Y1_k + Y2_{N-k}) + i (Y2_k - Y1_{N-k}) ]   (k >= 1,
+//     the factor 1/2 of Makhoul's formula is folded into the stored weights)
+//     u_m = sum_k U_k e^{+2 pi i m k / N}  ->  sigma1_{perm(m)} = Re u_m, sigma2_{perm(m)} = Im u_m,
+//     perm(m) = 2m for m < ceil(N/2), else 2(N-1-m)+1.
+// N a power of two: U is written in digit-reversed order and one in-place radix-8/4/2 DIT FFT of
+// length P = N runs in shared memory.  Any other N: Bluestein's chirp-z with P = pow2 >= 2N-1:
+//     a_k = U_k c_k,  c_j = e^{i pi j^2/N};  A = DIF-FFT_P(a);  A *= H (FFT of conj chirp, / P);
+//     DIT-IFFT_P;  u_m = c_m * conv_m.   DIF leaves its output digit-reversed, which is exactly what
+// the DIT consumes, so no reordering pass exists; the last DIF stage, the product with H and the
+// first DIT stage happen in registers.
+//
+// One CTA owns one (line, range of timestamp pairs) item and keeps G transforms in flight in shared
+// memory so that per-thread twiddles / modal constants are loaded once per G transforms.
+#pragma once
+#include "em_math.cuh"
+
+namespace em {
+
+// Per-distinct-N constant tables (built once per context, cached by N).
+struct NTab {
+  const double* lam;    // [N]   lambda_k = 2cos(k pi/N) - 2, computed by the HOST libm (see proton_em.cu)
+  const cplx* pre;      // [N]   pow2: e^{i pi k/2N};  Bluestein: e^{i pi (k + 2k^2)/(2N)}
+  const cplx* post;     // [N]   Bluestein only: c_m = e^{i pi m^2/N}
+  const cplx* hhat;     // [P]   Bluestein only: DIF-FFT_P of conj chirp, digit-reversed order, scaled 1/P
+  int n;
+  int log2p;            // FFT length class (0 = not on the in-CTA FFT path)
+  int bluestein;
+  int pad_;
+};
+
+struct EvalParams {
+  const int* class_lines;      // line ids of this class
+  int n_class_lines;
+  int chunks;                  // items per line
+  int pairs_per_chunk;
+  int T;
+  const int* num_nodes;
+  const double* a_coeff;
+  const long long* node_off;
+  const int* line_tab;         // line -> index into tabs
+  const NTab* tabs;
+  const double* W;             // [sum N] folded modal weights (forward kernel)
+  const double* ts;            // [T]
+  const cplx* tw;              // [P] e^{+2 pi i m/P}
+  const ulonglong2* exp_tab;   // [128]
+  double* stress;              // may be null (reduce-only)
+  double* mx;                  // [L*T]
+  int* amx;                    // [L*T]
+  unsigned char* flag;         // [L*T]
+  double critical;
+};
+
+// ---- small DFTs in registers ---------------------------------------------------------------------
+template <int SIGN> __device__ __forceinline__ cplx mul_i(cplx v) {   // v * (SIGN * i)
+  return SIGN > 0 ? cplx{-v.y, v.x} : cplx{v.y, -v.x};
+}
+template <int R, int SIGN> struct Dft;
+template <int SIGN> struct Dft<2, SIGN> {
+  static __device__ __forceinline__ void run(cplx (&v)[2]) {
+    const cplx a = v[0];
+    v[0] = cadd(a, v[1]); v[1] = csub(a, v[1]);
+  }
+};
+template <int SIGN> struct Dft<4, SIGN> {
+  static __device__ __forceinline__ void run(cplx (&v)[4]) {
+    const cplx a0 = cadd(v[0], v[2]), a1 = csub(v[0], v[2]);
+    const cplx b0 = cadd(v[1], v[3]), b1 = mul_i<SIGN>(csub(v[1], v[3]));
+    v[0] = cadd(a0, b0); v[2] = csub(a0, b0);
+    v[1] = cadd(a1, b1); v[3] = csub(a1, b1);
+  }
+};
+template <int SIGN> struct Dft<8, SIGN> {
+  static __device__ __forceinline__ void run(cplx (&v)[8]) {
+    cplx e[4] = {v[0], v[2], v[4], v[6]};
+    cplx o[4] = {v[1], v[3], v[5], v[7]};
+    Dft<4, SIGN>::run(e);
+    Dft<4, SIGN>::run(o);
+    constexpr double h = 0.70710678118654752440;
+    constexpr double s = (double)SIGN;
+    const cplx o1 = cplx{(o[1].x - s * o[1].y) * h, (s * o[1].x + o[1].y) * h};
+    const cplx o2 = mul_i<SIGN>(o[2]);
+    const cplx o3 = cplx{(-o[3].x - s * o[3].y) * h, (s * o[3].x - o[3].y) * h};
+    v[0] = cadd(e[0], o[0]); v[4] = csub(e[0], o[0]);
+    v[1] = cadd(e[1], o1);   v[5] = csub(e[1], o1);
+    v[2] = cadd(e[2], o2);   v[6] = csub(e[2], o2);
+    v[3] = cadd(e[3], o3);   v[7] = csub(e[3], o3);
+  }
+};
+
+// ---- stage plans: radices in DIF order (largest stride first); the first radix is always 8 --------
+__host__ __device__ constexpr int lg2(int r) { return r == 2 ? 1 : r == 4 ? 2 : r == 8 ? 3 : 4; }
+// LOG2P = 3*n8 + rem: n8 radix-8 stages followed by one radix-2 (rem 1) or radix-4 (rem 2) stage.
+__host__ __device__ constexpr int plan_n(int log2p) { return log2p / 3 + (log2p % 3 ? 1 : 0); }
+__host__ __device__ constexpr int plan_radix(int log2p, int i) {
+  return i < log2p / 3 ? 8 : (log2p % 3 == 1 ? 2 : 4);
+}
+template <int LOG2P, int I> __host__ __device__ constexpr int stage_radix() { return plan_radix(LOG2P, I); }
+template <int LOG2P, int I> __host__ __device__ constexpr int stage_log2s() {
+  int s = LOG2P;
+  for (int j = 0; j <= I; ++j) s -= lg2(plan_radix(LOG2P, j));
+  return s;
+}
+
+// Shared-memory index padding (units of 16-byte complex): one pad slot per 8 elements keeps the
+// stride-R accesses of the s = 1 stages conflict-free, one more per P/8 elements does the same for the
+// digit-reversed scatter of the power-of-two path.
+template <int LOG2P> __host__ __device__ constexpr int pad_idx(int p) { return p + (p >> 3) + (p >> (LOG2P - 3)); }
+template <int LOG2P> __host__ __device__ constexpr int padded_len() { return (1 << LOG2P) + (1 << (LOG2P - 3)) + 8; }
+
+// Position where DIF leaves output k (and where DIT expects input k).
+template <int LOG2P> __device__ __forceinline__ int digit_pos(int k) {
+  int p = 0;
+  int sh = LOG2P;
+#pragma unroll
+  for (int i = 0; i < plan_n(LOG2P); ++i) {
+    const int lr = lg2(plan_radix(LOG2P, i));
+    sh -= lr;
+    p |= (k & ((1 << lr) - 1)) << sh;
+    k >>= lr;
+  }
+  return p;
+}
+
+// Class configuration: threads per CTA and transforms in flight.
+template <int LOG2P, bool BLUE> struct Cfg {
+  static constexpr int P = 1 << LOG2P;
+  static constexpr int NT = LOG2P >= 13 ? 512 : LOG2P == 12 ? 256 : 128;
+  // rows of the staging buffer: N <= P (pow2) or N <= P/2 + 1 (Bluestein)
+  static constexpr int NSTAGE = BLUE ? (P / 2 + 8) : P;
+  static constexpr int G = LOG2P <= 6 ? 16 : LOG2P <= 8 ? 8 : LOG2P == 9 ? 4 : LOG2P == 10 ? 2 : 1;
+  static constexpr bool ALIAS_STAGE = LOG2P >= 12;       // staging rows reuse the data buffer
+  static constexpr size_t data_bytes = (size_t)G * padded_len<LOG2P>() * sizeof(cplx);
+  static constexpr size_t stage_bytes = ALIAS_STAGE ? 0 : (size_t)G * 2 * NSTAGE * sizeof(double);
+  static constexpr size_t smem_bytes = kExpTableEntries * sizeof(ulonglong2) + data_bytes + stage_bytes;
+};
+
+// One in-place stage over the G transforms in flight.
+//   DIF: y = DFT_R(x) then y_r *= w^(j r);   DIT: x_q *= w^(j q) then DFT_R.   w = e^{SIGN 2 pi i / (R S)}.
+template <int LOG2P, int RADIX, int LOG2S, bool DIF, int SIGN, int NT>
+__device__ __forceinline__ void fft_stage(cplx* __restrict__ data, int gcount, const cplx* __restrict__ tw, int tid) {
+  constexpr int P = 1 << LOG2P, S = 1 << LOG2S, LOG2R = lg2(RADIX), NB = P / RADIX;
+  constexpr int TWMUL = P / (RADIX * S);
+  constexpr int BSTEP = NB < NT ? NB : NT;
+  constexpr int GSTEP = NB < NT ? NT / NB : 1;
+  constexpr int TSTRIDE = padded_len<LOG2P>();
+  const int g0 = NB < NT ? tid / NB : 0;
+  for (int b = (NB < NT ? tid % NB : tid); b < NB; b += BSTEP) {
+    const int j = b & (S - 1);
+    const int base = ((b >> LOG2S) << (LOG2S + LOG2R)) | j;
+    cplx w[RADIX];
+    if (S > 1) {
+#pragma unroll
+      for (int q = 1; q < RADIX; ++q) {
+        const cplx tv = ldg_cplx(tw + j * q * TWMUL);
+        w[q] = cplx{tv.x, SIGN > 0 ? tv.y : -tv.y};
+      }
+    }
+    for (int g = g0; g < gcount; g += GSTEP) {
+      cplx* d = data + g * TSTRIDE;
+      cplx v[RADIX];
+#pragma unroll
+      for (int q = 0; q < RADIX; ++q) v[q] = d[pad_idx<LOG2P>(base + q * S)];
+      if (DIF) {
+        Dft<RADIX, SIGN>::run(v);
+        if (S > 1) {
+#pragma unroll
+          for (int q = 1; q < RADIX; ++q) v[q] = cmul(v[q], w[q]);
+        }
+      } else {
+        if (S > 1) {
+#pragma unroll
+          for (int q = 1; q < RADIX; ++q) v[q] = cmul(v[q], w[q]);
+        }
+        Dft<RADIX, SIGN>::run(v);
+      }
+#pragma unroll
+      for (int q = 0; q < RADIX; ++q) d[pad_idx<LOG2P>(base + q * S)] = v[q];
+    }
+  }
+}
+
+// Middle of Bluestein: last DIF stage (s = 1), product with H, first DIT stage (s = 1) in registers.
+template <int LOG2P, int RADIX, int NT>
+__device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, const cplx* __restrict__ hhat, int tid) {
+  constexpr int P = 1 << LOG2P, NB = P / RADIX;
+  constexpr int BSTEP = NB < NT ? NB : NT;
+  constexpr int GSTEP = NB < NT ? NT / NB : 1;
+  constexpr int TSTRIDE = padded_len<LOG2P>();
+  const int g0 = NB < NT ? tid / NB : 0;
+  for (int b = (NB < NT ? tid % NB : tid); b < NB; b += BSTEP) {
+    const int base = b * RADIX;
+    cplx h[RADIX];
+#pragma unroll
+    for (int q = 0; q < RADIX; ++q) h[q] = ldg_cplx(hhat + base + q);
+    for (int g = g0; g < gcount; g += GSTEP) {
+      cplx* d = data + g * TSTRIDE;
+      cplx v[RADIX];
+#pragma unroll
+      for (int q = 0; q < RADIX; ++q) v[q] = d[pad_idx<LOG2P>(base + q)];
+      Dft<RADIX, -1>::run(v);
+#pragma unroll
+      for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], h[q]);
+      Dft<RADIX, +1>::run(v);
+#pragma unroll
+      for (int q = 0; q < RADIX; ++q) d[pad_idx<LOG2P>(base + q)] = v[q];
+    }
+  }
+}
+
+// Stage recursion helpers (compile-time unrolled over the plan).
+template <int LOG2P, int I, int IEND, int NT> struct DifStages {   // stages I .. IEND-1, SIGN = -1
+  static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
+    if constexpr (I < IEND) {
+      fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), true, -1, NT>(data, gcount, tw, tid);
+      __syncthreads();
+      DifStages<LOG2P, I + 1, IEND, NT>::run(data, gcount, tw, tid);
+    }
+  }
+};
+template <int LOG2P, int I, int ISTOP, int NT> struct DitStages {   // stages I down to ISTOP, SIGN = +1
+  static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
+    if constexpr (I >= ISTOP) {
+      fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), false, +1, NT>(data, gcount, tw, tid);
+      __syncthreads();
+      DitStages<LOG2P, I - 1, ISTOP, NT>::run(data, gcount, tw, tid);
+    }
+  }
+};
+
+template <int LOG2P, bool BLUE>
+__global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT)
+em_eval_fft_kernel(const EvalParams prm) {
+  using C = Cfg<LOG2P, BLUE>;
+  constexpr int P = C::P, NT = C::NT, G = C::G, NST = plan_n(LOG2P);
+  constexpr int TSTRIDE = padded_len<LOG2P>();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  ulonglong2* exp_tab = reinterpret_cast<ulonglong2*>(smem_raw);
+  cplx* data = reinterpret_cast<cplx*>(smem_raw + kExpTableEntries * sizeof(ulonglong2));
+  double* stage = C::ALIAS_STAGE ? reinterpret_cast<double*>(data)
+                                 : reinterpret_cast<double*>(smem_raw + kExpTableEntries * sizeof(ulonglong2) + C::data_bytes);
+  const int tid = threadIdx.x;
+  for (int i = tid; i < kExpTableEntries; i += NT) exp_tab[i] = prm.exp_tab[i];
+
+  const int item = blockIdx.x;
+  const int li = item / prm.chunks, chunk = item - li * prm.chunks;
+  const int line = prm.class_lines[li];
+  const int N = prm.num_nodes[line];
+  const double a = prm.a_coeff[line];
+  const long long noff = prm.node_off[line];
+  const NTab tab = prm.tabs[prm.line_tab[line]];
+  const double* __restrict__ lam = tab.lam;
+  const double* __restrict__ W = prm.W + noff;
+  const int T = prm.T;
+  const int npairs = (T + 1) >> 1;
+  const int pair_begin = chunk * prm.pairs_per_chunk;
+  const int pair_end = min(npairs, pair_begin + prm.pairs_per_chunk);
+  const int K2 = (N >> 1) + 1;
+  const int halfN = (N + 1) >> 1;
+  __syncthreads();
+
+  for (int pb = pair_begin; pb < pair_end; pb += G) {
+    const int gcount = min(G, pair_end - pb);
+    // ---- phase 1: modal values -> packed complex spectrum U in shared memory -------------------
+    {
+      int kp0, kstep, g0, gstep;
+      if (K2 >= NT) { kp0 = tid; kstep = NT; g0 = 0; gstep = 1; }
+      else {
+        const int groups = NT / K2;
+        kp0 = tid % K2; kstep = K2; g0 = tid / K2; gstep = groups;
+        if (g0 >= groups) kp0 = K2;
+      }
+      for (int kp = kp0; kp < K2; kp += kstep) {
+        const int k = kp, kk = N - kp;
+        const bool single = (kp == 0) || (kk == k);
+        const double lamk = lam[k], wk = W[k];
+        double lamkk = 0.0, wkk = 0.0;
+        cplx prek = cplx{1.0, 0.0}, prekk = cplx{1.0, 0.0};
+        if (kp != 0) prek = ldg_cplx(tab.pre + k);
+        if (!single) { lamkk = lam[kk]; wkk = W[kk]; prekk = ldg_cplx(tab.pre + kk); }
+        const int posk = pad_idx<LOG2P>(BLUE ? k : digit_pos<LOG2P>(k));
+        const int poskk = single ? 0 : pad_idx<LOG2P>(BLUE ? kk : digit_pos<LOG2P>(kk));
+        for (int g = g0; g < gcount; g += gstep) {
+          const int j1 = 2 * (pb + g);
+          const double t1 = prm.ts[j1];
+          const double t2 = (j1 + 1 < T) ? prm.ts[j1 + 1] : t1;
+          const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
+          cplx* d = data + g * TSTRIDE;
+          const double y1k = em_modal(lamk, wk, w1, t1, exp_tab);
+          const double y2k = em_modal(lamk, wk, w2, t2, exp_tab);
+          if (kp == 0) {
+            d[posk] = cplx{y1k, y2k};
+          } else if (single) {
+            d[posk] = cmul(prek, cplx{y1k + y2k, y2k - y1k});
+          } else {
+            const double y1kk = em_modal(lamkk, wkk, w1, t1, exp_tab);
+            const double y2kk = em_modal(lamkk, wkk, w2, t2, exp_tab);
+            d[posk] = cmul(prek, cplx{y1k + y2kk, y2k - y1kk});
+            d[poskk] = cmul(prekk, cplx{y1kk + y2k, y2kk - y1k});
+          }
+        }
+      }
+      if (BLUE) {
+        const int nz = P - N;
+        for (int e = tid; e < gcount * nz; e += NT) {
+          const int g = e / nz, p = N + (e - g * nz);
+          data[g * TSTRIDE + pad_idx<LOG2P>(p)] = cplx{0.0, 0.0};
+        }
+      }
+    }
+    __syncthreads();
+    // ---- phase 2: transforms ------------------------------------------------------------------
+    if (BLUE) {
+      DifStages<LOG2P, 0, NST - 1, NT>::run(data, gcount, prm.tw, tid);
+      fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, gcount, tab.hhat, tid);
+      __syncthreads();
+      DitStages<LOG2P, NST - 2, 1, NT>::run(data, gcount, prm.tw, tid);
+    } else {
+      DitStages<LOG2P, NST - 1, 1, NT>::run(data, gcount, prm.tw, tid);
+    }
+    // ---- last DIT stage (radix 8, stride P/8) fused with chirp post-multiply + de-interleave ---
+    {
+      constexpr int S = P / 8, NB = P / 8;
+      constexpr int QN = BLUE ? 4 : 8;          // Bluestein: only outputs m < N <= P/2 are wanted
+      if constexpr (!C::ALIAS_STAGE) {
+        constexpr int BSTEP = NB < NT ? NB : NT;
+        constexpr int GSTEP = NB < NT ? NT / NB : 1;
+        const int g0 = NB < NT ? tid / NB : 0;
+        for (int b = (NB < NT ? tid % NB : tid); b < NB; b += BSTEP) {
+          const int j = b;
+          cplx w[8];
+#pragma unroll
+          for (int q = 1; q < 8; ++q) w[q] = ldg_cplx(prm.tw + j * q);
+          cplx post[QN];
+          if (BLUE) {
+#pragma unroll
+            for (int q = 0; q < QN; ++q) {
+              const int m = j + q * S;
+              post[q] = cplx{1.0, 0.0};
+              if (m < N) post[q] = ldg_cplx(tab.post + m);
+            }
+          }
+          for (int g = g0; g < gcount; g += GSTEP) {
+            cplx* d = data + g * TSTRIDE;
+            cplx v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = d[pad_idx<LOG2P>(j + q * S)];
+#pragma unroll
+            for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
+            Dft<8, +1>::run(v);
+            double* s1 = stage + (size_t)g * 2 * C::NSTAGE;
+            double* s2 = s1 + C::NSTAGE;
+#pragma unroll
+            for (int q = 0; q < QN; ++q) {
+              const int m = j + q * S;
+              if (m < N) {
+                const cplx u = BLUE ? cmul(v[q], post[q]) : v[q];
+                const int idx = (m < halfN) ? 2 * m : 2 * (N - 1 - m) + 1;
+                s1[idx] = u.x; s2[idx] = u.y;
+              }
+            }
+          }
+        }
+      } else {
+        // G == 1 and the staging rows live inside the data buffer: keep results in registers across a
+        // barrier, then overwrite the buffer.
+        static_assert(!C::ALIAS_STAGE || (G == 1 && NB % NT == 0), "alias staging needs G == 1");
+        constexpr int ITERS = NB / NT;
+        cplx vv[ITERS][QN];
+#pragma unroll
+        for (int it = 0; it < ITERS; ++it) {
+          const int j = tid + it * NT;
+          cplx v[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) v[q] = data[pad_idx<LOG2P>(j + q * S)];
+#pragma unroll
+          for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], ldg_cplx(prm.tw + j * q));
+          Dft<8, +1>::run(v);
+#pragma unroll
+          for (int q = 0; q < QN; ++q) {
+            const int m = j + q * S;
+            vv[it][q] = v[q];
+            if (BLUE && m < N) vv[it][q] = cmul(v[q], ldg_cplx(tab.post + m));
+          }
+        }
+        __syncthreads();
+        double* s1 = stage;
+        double* s2 = s1 + C::NSTAGE;
+#pragma unroll
+        for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+          for (int q = 0; q < QN; ++q) {
+            const int m = tid + it * NT + q * S;
+            if (m < N) {
+              const int idx = (m < halfN) ? 2 * m : 2 * (N - 1 - m) + 1;
+              s1[idx] = vv[it][q].x; s2[idx] = vv[it][q].y;
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- phase 3: one warp per (transform, timestamp) row: coalesced store + max / argmax -------
+    {
+      const int warp = tid >> 5, lane = tid & 31, nwarps = NT >> 5;
+      for (int rr = warp; rr < 2 * gcount; rr += nwarps) {
+        const int g = rr >> 1, which = rr & 1;
+        const int tj = 2 * (pb + g) + which;
+        if (tj >= T) continue;
+        const double* src = stage + (size_t)g * 2 * C::NSTAGE + (size_t)which * C::NSTAGE;
+        double* dst = prm.stress ? prm.stress + noff * (long long)T + (long long)tj * N : nullptr;
+        double best = -__longlong_as_double(0x7ff0000000000000LL);
+        int besti = 0x7fffffff;
+        for (int n = lane; n < N; n += 32) {
+          const double v = src[n];
+          if (dst) __stcs(dst + n, v);
+          if (v > best) { best = v; besti = n; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+          const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+          if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+        }
+        if (lane == 0) {
+          if (besti == 0x7fffffff) { besti = 0; best = src[0]; }
+          const long long o = (long long)line * T + tj;
+          prm.mx[o] = best; prm.amx[o] = besti;
+          prm.flag[o] = (best > prm.critical) ? 1 : 0;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace em
