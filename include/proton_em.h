@@ -1,0 +1,129 @@
+/* proton_em.h — C ABI of libproton_em.so, the B200 (sm_100a) drop-in for the line-analysis hot path
+ * of oaxelou/PROTON: what `bin/EMtool_analytical` computes per interconnect line.
+ *
+ * Plain C: pointers and sizes only, no torch / C++ types.  Every function returns 0 on success or
+ * a negative PROTON_EM_E* code; the message is available from proton_em_last_error() (thread-local).
+ * Nothing here throws or calls exit().
+ *
+ * Level 1 (process-compatible): proton_em_run_cfg() does exactly what the reference process does for
+ * one analytical.cfg; bin/EMtool_analytical (built from proton_b200/csrc/emtool_main.cpp) wraps it.
+ * Level 2 (batched, new — the reference has no batch API): pack a ragged batch of lines once, then
+ * evaluate it at any number of timestamps.
+ */
+#ifndef PROTON_EM_H
+#define PROTON_EM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PROTON_EM_OK 0
+#define PROTON_EM_EINVAL (-1)   /* bad argument / malformed input (reference: message + exit(1)) */
+#define PROTON_EM_ENOMEM (-2)
+#define PROTON_EM_ECUDA (-3)    /* CUDA runtime error, or no usable device */
+#define PROTON_EM_EIO (-4)      /* file missing / unreadable / unwritable */
+
+#define PROTON_EM_HOST 0        /* pointer arguments are host memory */
+#define PROTON_EM_DEVICE 1      /* pointer arguments are device memory on the ctx's device */
+
+#define PROTON_EM_ALG_AUTO 0    /* short-line / FFT / long-line kernels chosen per line length */
+#define PROTON_EM_ALG_DIRECT 1  /* O(N^2) cosine sums for every line (cross-check only, slow) */
+
+typedef struct proton_em_ctx proton_em_ctx;
+typedef struct proton_em_plan proton_em_plan;
+
+/* A ragged batch of lines: for line l, the inputs the reference kernel reads from disk —
+ *   num_nodes[l], a_coeff[l]      `num_nodes`, `A_coeff` of analytical.cfg
+ *                                 (analytical_class_cli.py:53-57; read_file, bin/EMtool_analytical@0xaaf4)
+ *   triplets [trip_off[l], trip_off[l+1])   rows of B.csv `row,col,value`
+ *                                 (matrix_formulation_func_cli.py:240-252; tripletParser @0xb010)
+ *   curden   [u_off[l], u_off[l+1])         lines of curden.csv (:268-273; analyical_wrapper @0xba39)
+ * Triplets may be unsorted and may repeat a (row, col): repeats are summed, as Eigen's
+ * setFromTriplets does in the reference (@0xbbfe). */
+typedef struct proton_em_batch {
+  int64_t num_lines;
+  const int32_t* num_nodes;   /* [L] */
+  const double* a_coeff;      /* [L] */
+  const int64_t* trip_off;    /* [L+1] */
+  const int32_t* trip_row;
+  const int32_t* trip_col;
+  const double* trip_val;
+  const int64_t* u_off;       /* [L+1] */
+  const double* curden;
+} proton_em_batch;
+
+typedef struct proton_em_opts {
+  double critical_stress;     /* flag = max > critical (PROTON_cli.py:1063); NaN: all flags 0 */
+  int32_t algorithm;          /* PROTON_EM_ALG_* */
+  int32_t reserved;
+} proton_em_opts;
+
+/* Outputs for L lines at T timestamps.
+ *   stress      sum_l N_l * T doubles; line l starts at node_off[l]*T and is [T][N_l] row-major, i.e.
+ *               row j is the content of the reference's stress_<t_j>.txt (analyical_wrapper @0xbca3).
+ *               May be NULL ("reduce-only": nothing but the reductions is written).
+ *   max_stress  [L*T]  max over the nodes of a row (PROTON_cli.py:1058-1061)
+ *   argmax      [L*T]  first node attaining it (PROTON_cli.py:861-867)
+ *   flag        [L*T]  max_stress > critical_stress (PROTON_cli.py:1063) */
+typedef struct proton_em_result {
+  double* stress;
+  double* max_stress;
+  int32_t* argmax;
+  uint8_t* flag;
+} proton_em_result;
+
+/* Context: one per (process, device); owns a stream, the constant tables and a cache of per-length
+ * tables (lambda_k from the host libm, chirps, transformed chirps).  Not thread-safe; distinct
+ * contexts are independent. */
+int proton_em_create(proton_em_ctx** out, int device);
+int proton_em_destroy(proton_em_ctx* ctx);
+const char* proton_em_last_error(void);
+const char* proton_em_version(void);
+
+/* Pack: validates the batch, computes r = B*u per line and the forward DCT, and leaves the
+ * time-independent modal weights resident in device memory.  Replaces form_analytical_solution +
+ * dct1d (bin/EMtool_analytical@0xc46c, @0xc156).  `location` says where the batch arrays live.
+ * Synchronous (it builds host-side tables and reports input errors). */
+int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* batch, int location, proton_em_plan** out);
+int proton_em_plan_destroy(proton_em_plan* plan);
+int64_t proton_em_plan_total_nodes(const proton_em_plan* plan);
+int64_t proton_em_plan_num_lines(const proton_em_plan* plan);
+/* Device scratch the plan holds (bytes) — modal weights, packed r, per-line tables. */
+int64_t proton_em_plan_scratch_bytes(const proton_em_plan* plan);
+
+/* Evaluate a packed batch at T timestamps (seconds).  Replaces calc_analytical_solution + idct1d
+ * (@0xc68c, @0xc2a0) and the max / threshold consumers.  `ts` and the result arrays are device
+ * pointers when location == PROTON_EM_DEVICE (work is queued on the ctx stream and the call
+ * returns without synchronising), host pointers otherwise (the call copies and synchronises). */
+int proton_em_eval(proton_em_plan* plan, const double* ts, int32_t T, const proton_em_opts* opts,
+                   const proton_em_result* result, int location);
+int proton_em_synchronize(proton_em_ctx* ctx);
+/* CUDA stream (cudaStream_t) all of the ctx's work is queued on, for callers that time with events. */
+void* proton_em_stream(proton_em_ctx* ctx);
+/* Number of kernel launches issued by this ctx so far (bench.py reports it as gpu_launches). */
+int64_t proton_em_launch_count(const proton_em_ctx* ctx);
+
+/* One call for host callers: pack + eval + copy back, splitting the batch so that the device-side
+ * stress buffer stays below max_device_bytes (0 = default).  This is the end-to-end path bench.py
+ * times as `e2e`. */
+int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* batch, const double* ts, int32_t T,
+                           const proton_em_opts* opts, const proton_em_result* result,
+                           int64_t max_device_bytes);
+
+/* Level 1: the reference process.  Reads `cfg_path` (keys input_files, num_nodes, A_coeff,
+ * simulation_time; read_file @0xaaf4), <input_files>/curden.csv and <input_files>/B.csv, computes the
+ * stress at simulation_time and writes <input_files with the first "input" replaced by "output">/
+ * stress_<%f of t>.txt with one "%.18g" value per line (analyical_wrapper @0xb93c-0xbec0).  On failure
+ * `msg` receives the text the reference prints to stdout before exit(1). */
+int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_t msg_len);
+
+/* Test hook: y[i] = the device exp() used by the modal evaluation (must equal the host libm's). */
+int proton_em_debug_exp(proton_em_ctx* ctx, const double* x_host, double* y_host, int64_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PROTON_EM_H */

@@ -1,0 +1,379 @@
+// em_kernels.cuh — packing (B*u), forward DCT, constant tables, short-line and direct evaluators.
+//
+// Reference functions replaced: Eigen SpMV in form_analytical_solution
+// (bin/EMtool_analytical@0xc46c), dct1d (@0xc156), and for short lines calc_analytical_solution +
+// idct1d (@0xc68c, @0xc2a0) plus the max / threshold consumers (PROTON_cli.py:1058-1066).
+#pragma once
+#include "em_fft.cuh"
+
+namespace em {
+
+// ---------------------------------------------------------------------------------------------
+// (a) Packing: r = B*u per line, with Eigen's semantics for a column-major SparseMatrix built by
+// setFromTriplets: duplicates are summed first (in input order), then for every stored (row, col),
+// columns ascending, res[row] += value * u[col] with two roundings (no FMA).  Output is the sparse
+// vector r as sorted unique rows; r_idx / r_val use the triplet offsets as capacity.
+// One CTA per line; ranks are found by counting (O(nnz^2 / 128), nnz = 2S is a few hundred at most).
+// ---------------------------------------------------------------------------------------------
+struct PackParams {
+  long long num_lines;
+  const int* num_nodes;
+  const long long* trip_off;
+  const int* trip_row;
+  const int* trip_col;
+  const double* trip_val;
+  const long long* u_off;
+  const double* curden;
+  int* perm;          // [ntrip] scratch: sorted position -> triplet
+  double* prod;       // [ntrip] scratch
+  int* r_idx;         // [ntrip]
+  double* r_val;      // [ntrip]
+  int* r_cnt;         // [L]
+  int* error_flag;    // set to 1 + line on a bad index
+};
+
+__device__ __forceinline__ bool trip_less(int ra, int ca, int ia, int rb, int cb, int ib) {
+  if (ra != rb) return ra < rb;
+  if (ca != cb) return ca < cb;
+  return ia < ib;
+}
+
+__global__ void __launch_bounds__(128) em_pack_kernel(const PackParams p) {
+  __shared__ int bad;
+  for (long long line = blockIdx.x; line < p.num_lines; line += gridDim.x) {
+    const long long t0 = p.trip_off[line];
+    const int nt = (int)(p.trip_off[line + 1] - t0);
+    const int N = p.num_nodes[line];
+    const int S = (int)(p.u_off[line + 1] - p.u_off[line]);
+    const int* row = p.trip_row + t0;
+    const int* col = p.trip_col + t0;
+    const double* val = p.trip_val + t0;
+    const double* u = p.curden + p.u_off[line];
+    int* perm = p.perm + t0;
+    double* prod = p.prod + t0;
+    if (threadIdx.x == 0) bad = (N <= 0) ? 1 : 0;
+    __syncthreads();
+    // 1. rank by (row, col, input order)
+    for (int i = threadIdx.x; i < nt; i += blockDim.x) {
+      const int ri = row[i], ci = col[i];
+      if (ri < 0 || ri >= N || ci < 0 || ci >= S) bad = 1;
+      int rank = 0;
+      for (int j = 0; j < nt; ++j) rank += trip_less(row[j], col[j], j, ri, ci, i) ? 1 : 0;
+      perm[rank] = i;
+    }
+    __syncthreads();
+    if (bad) {                       // uniform: every thread reads the same shared flag
+      if (threadIdx.x == 0) { p.r_cnt[line] = 0; atomicMax(p.error_flag, (int)min(line + 1, (long long)0x7fffffff)); }
+      __syncthreads();
+      continue;
+    }
+    // 2. per (row, col) group: sum duplicates in input order, multiply by u[col]
+    for (int s = threadIdx.x; s < nt; s += blockDim.x) {
+      const int i = perm[s];
+      const bool start = (s == 0) || row[perm[s - 1]] != row[i] || col[perm[s - 1]] != col[i];
+      if (start) {
+        double v = val[i];
+        for (int q = s + 1; q < nt && row[perm[q]] == row[i] && col[perm[q]] == col[i]; ++q) v = __dadd_rn(v, val[perm[q]]);
+        prod[s] = __dmul_rn(v, u[col[i]]);
+      }
+    }
+    __syncthreads();
+    // 3. per row: accumulate its products in ascending column order, compact the rows
+    for (int s = threadIdx.x; s < nt; s += blockDim.x) {
+      const int i = perm[s];
+      const bool row_start = (s == 0) || row[perm[s - 1]] != row[i];
+      if (row_start) {
+        int before = 0;
+        for (int q = 1; q <= s; ++q) before += (row[perm[q - 1]] != row[perm[q]]) ? 1 : 0;
+        double acc = 0.0;
+        for (int q = s; q < nt && row[perm[q]] == row[i]; ++q) {
+          const bool gstart = (q == s) || col[perm[q - 1]] != col[perm[q]];
+          if (gstart) acc = __dadd_rn(acc, prod[q]);
+        }
+        p.r_idx[t0 + before] = row[i];
+        p.r_val[t0 + before] = acc;
+      }
+    }
+    if (threadIdx.x == 0) {
+      int cnt = nt > 0 ? 1 : 0;
+      for (int q = 1; q < nt; ++q) cnt += (row[perm[q - 1]] != row[perm[q]]) ? 1 : 0;
+      p.r_cnt[line] = cnt;
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// (b) Forward DCT-II of the sparse r, folded with everything that does not depend on time:
+//   R_k = sum_v r_v cos(pi (2v+1) k / (2N))            (exact integer angle reduction)
+//   W_k = R_k / N                      if k == 0 or lambda_k == 0   (then Yhat_k = t * W_k)
+//       = R_k / (N * (lambda_k * a))   otherwise                    (then Yhat_k = (e^{lambda_k a t} - 1) W_k)
+// which equals the reference's q_k, the 1/(lambda a) of D_kk, the sqrt scalings of dct1d/idct1d and
+// Makhoul's 1/2, all in one number per mode.  One thread per (line, mode).
+// ---------------------------------------------------------------------------------------------
+struct ForwardParams {
+  long long num_lines;
+  long long total_nodes;
+  const int* num_nodes;
+  const double* a_coeff;
+  const long long* node_off;
+  const long long* trip_off;
+  const int* r_idx;
+  const double* r_val;
+  const int* r_cnt;
+  const int* line_tab;
+  const NTab* tabs;
+  double* W;
+};
+
+__device__ __forceinline__ long long find_line(const long long* __restrict__ off, long long L, long long g) {
+  long long lo = 0, hi = L;           // off[lo] <= g < off[hi]
+  while (hi - lo > 1) {
+    const long long mid = (lo + hi) >> 1;
+    if (off[mid] <= g) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(256) em_forward_kernel(const ForwardParams p) {
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < p.total_nodes;
+       g += (long long)gridDim.x * blockDim.x) {
+    const long long line = find_line(p.node_off, p.num_lines, g);
+    const int N = p.num_nodes[line];
+    const int k = (int)(g - p.node_off[line]);
+    const long long t0 = p.trip_off[line];
+    const int cnt = p.r_cnt[line];
+    const unsigned long long den = 2ULL * (unsigned long long)N;
+    double R = 0.0;
+    for (int i = 0; i < cnt; ++i) {
+      const unsigned long long v = (unsigned long long)p.r_idx[t0 + i];
+      const unsigned long long num = ((2ULL * v + 1ULL) * (unsigned long long)k) % (2ULL * den);
+      R = fma(p.r_val[t0 + i], em_cos_frac(num, den), R);
+    }
+    const double lam = p.tabs[p.line_tab[line]].lam[k];
+    double w = R / (double)N;
+    if (lam != 0.0) w = w / __dmul_rn(lam, p.a_coeff[line]);
+    p.W[g] = w;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Constant tables per distinct N on the in-CTA FFT path (see NTab).
+// ---------------------------------------------------------------------------------------------
+struct TableParams {
+  const NTab* tabs;       // entries handled by this launch (all share LOG2P / BLUE); pre/post/hhat writable
+  const cplx* tw;
+};
+
+template <int LOG2P, bool BLUE>
+__global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT) em_tables_kernel(const TableParams p) {
+  constexpr int P = 1 << LOG2P, NT = Cfg<LOG2P, BLUE>::NT;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* data = reinterpret_cast<cplx*>(smem_raw);
+  const NTab tab = p.tabs[blockIdx.x];
+  const unsigned long long N = (unsigned long long)tab.n;
+  cplx* pre = const_cast<cplx*>(tab.pre);
+  const int tid = threadIdx.x;
+  if (!BLUE) {
+    for (int k = tid; k < (int)N; k += NT) pre[k] = em_cis_frac((unsigned long long)k, 2ULL * N);
+    return;
+  }
+  cplx* post = const_cast<cplx*>(tab.post);
+  cplx* hhat = const_cast<cplx*>(tab.hhat);
+  for (int k = tid; k < (int)N; k += NT) {
+    const unsigned long long kk = (unsigned long long)k;
+    pre[k] = em_cis_frac((kk + 2ULL * kk * kk) % (4ULL * N), 2ULL * N);
+    post[k] = em_cis_frac((kk * kk) % (2ULL * N), N);
+  }
+  for (int i = tid; i < P; i += NT) data[pad_idx<LOG2P>(i)] = cplx{0.0, 0.0};
+  __syncthreads();
+  const double inv_p = 1.0 / (double)P;
+  for (int j = tid; j < (int)N; j += NT) {
+    const unsigned long long jj = (unsigned long long)j;
+    const cplx c = em_cis_frac((jj * jj) % (2ULL * N), N);
+    const cplx h = cplx{c.x * inv_p, -c.y * inv_p};
+    data[pad_idx<LOG2P>(j)] = h;
+    if (j) data[pad_idx<LOG2P>(P - j)] = h;
+  }
+  __syncthreads();
+  DifStages<LOG2P, 0, plan_n(LOG2P), NT>::run(data, 1, p.tw, tid);
+  for (int i = tid; i < P; i += NT) hhat[i] = data[pad_idx<LOG2P>(i)];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Short lines (N <= 32): one warp per (line, chunk of timestamps); lane n owns node n, lane k
+// evaluates mode k, a per-warp table holds cos(pi m / 2N), m in [0, 4N).
+// ---------------------------------------------------------------------------------------------
+constexpr int kSmallMaxN = 32;
+
+struct SmallParams {
+  const int* class_lines;
+  int n_class_lines;
+  int chunks;
+  int ts_per_chunk;
+  int T;
+  const int* num_nodes;
+  const double* a_coeff;
+  const long long* node_off;
+  const int* line_tab;
+  const NTab* tabs;
+  const double* W;
+  const double* ts;
+  const ulonglong2* exp_tab;
+  double* stress;
+  double* mx;
+  int* amx;
+  unsigned char* flag;
+  double critical;
+};
+
+__global__ void __launch_bounds__(128) em_eval_small_kernel(const SmallParams p) {
+  __shared__ ulonglong2 exp_tab[kExpTableEntries];
+  __shared__ double ctab[4][4 * kSmallMaxN];
+  for (int i = threadIdx.x; i < kExpTableEntries; i += blockDim.x) exp_tab[i] = p.exp_tab[i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long item = (long long)blockIdx.x * 4 + warp;
+  if (item >= (long long)p.n_class_lines * p.chunks) return;
+  const int li = (int)(item / p.chunks), chunk = (int)(item - (long long)li * p.chunks);
+  const int line = p.class_lines[li];
+  const int N = p.num_nodes[line];
+  const double a = p.a_coeff[line];
+  const long long noff = p.node_off[line];
+  double* ct = ctab[warp];
+  for (int m = lane; m < 4 * N; m += 32) ct[m] = em_cos_frac((unsigned long long)m, 2ULL * N);
+  __syncwarp();
+  double lam = 0.0, wk = 0.0;
+  if (lane < N) {
+    lam = p.tabs[p.line_tab[line]].lam[lane];
+    wk = p.W[noff + lane];
+    if (lane > 0) wk = wk + wk;     // W carries Makhoul's 1/2 for k >= 1; the plain cosine sum does not want it
+  }
+  const int j0 = chunk * p.ts_per_chunk, j1 = min(p.T, j0 + p.ts_per_chunk);
+  const int step = 2 * lane + 1;
+  const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+  for (int j = j0; j < j1; ++j) {
+    const double t = p.ts[j];
+    const double w = __dmul_rn(a, t);
+    const double y = (lane < N) ? em_modal(lam, wk, w, t, exp_tab) : 0.0;
+    double acc = 0.0;
+    int m = 0;
+    for (int k = 0; k < N; ++k) {
+      const double yk = __shfl_sync(0xffffffffu, y, k);
+      if (lane < N) acc = fma(yk, ct[m], acc);
+      m += step;
+      if (m >= 4 * N) m -= 4 * N;
+    }
+    double best = ninf;
+    int besti = 0x7fffffff;
+    if (lane < N && acc > ninf) { best = acc; besti = lane; }
+    if (p.stress && lane < N) __stcs(p.stress + noff * (long long)p.T + (long long)j * N + lane, acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+      if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+    }
+    const double first = __shfl_sync(0xffffffffu, acc, 0);
+    if (lane == 0) {
+      if (besti == 0x7fffffff) { besti = 0; best = first; }
+      const long long o = (long long)line * p.T + j;
+      p.mx[o] = best; p.amx[o] = besti; p.flag[o] = (best > p.critical) ? 1 : 0;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Direct O(N^2) evaluator for any N: one CTA per (line, timestamp).  Not a production path — it is
+// the device-side cross-check the tests use (opts.algorithm = DIRECT), with every cosine obtained
+// from an exactly reduced angle.
+// ---------------------------------------------------------------------------------------------
+struct DirectParams {
+  long long num_lines;
+  int T;
+  const int* num_nodes;
+  const double* a_coeff;
+  const long long* node_off;
+  const int* line_tab;
+  const NTab* tabs;
+  const double* W;
+  const double* ts;
+  const ulonglong2* exp_tab;
+  double* stress;
+  double* mx;
+  int* amx;
+  unsigned char* flag;
+  double critical;
+};
+
+__global__ void __launch_bounds__(256) em_eval_direct_kernel(const DirectParams p) {
+  constexpr int KC = 512;
+  __shared__ ulonglong2 exp_tab[kExpTableEntries];
+  __shared__ double ych[KC];
+  __shared__ double red_v[8];
+  __shared__ int red_i[8];
+  __shared__ double first_s;
+  for (int i = threadIdx.x; i < kExpTableEntries; i += blockDim.x) exp_tab[i] = p.exp_tab[i];
+  __syncthreads();
+  const long long line = blockIdx.x / p.T;
+  const int j = (int)(blockIdx.x - line * p.T);
+  const int N = p.num_nodes[line];
+  const double a = p.a_coeff[line];
+  const long long noff = p.node_off[line];
+  const double* lam = p.tabs[p.line_tab[line]].lam;
+  const double t = p.ts[j];
+  const double w = __dmul_rn(a, t);
+  const unsigned long long den = 2ULL * (unsigned long long)N;
+  double best = -__longlong_as_double(0x7ff0000000000000LL);
+  int besti = 0x7fffffff;
+  for (int n0 = 0; n0 < N; n0 += 256) {
+    const int n = n0 + threadIdx.x;
+    double acc = 0.0;
+    for (int k0 = 0; k0 < N; k0 += KC) {
+      __syncthreads();
+      for (int k = k0 + threadIdx.x; k < min(N, k0 + KC); k += 256) {
+        double wk = p.W[noff + k];
+        if (k > 0) wk = wk + wk;
+        ych[k - k0] = em_modal(lam[k], wk, w, t, exp_tab);
+      }
+      __syncthreads();
+      if (n < N) {
+        for (int k = k0; k < min(N, k0 + KC); ++k) {
+          const unsigned long long num = ((unsigned long long)k * (2ULL * n + 1ULL)) % (2ULL * den);
+          acc = fma(ych[k - k0], em_cos_frac(num, den), acc);
+        }
+      }
+    }
+    if (n < N) {
+      if (p.stress) p.stress[noff * (long long)p.T + (long long)j * N + n] = acc;
+      if (acc > best) { best = acc; besti = n; }
+      if (n == 0) first_s = acc;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+    if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { red_v[threadIdx.x >> 5] = best; red_i[threadIdx.x >> 5] = besti; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int q = 1; q < 8; ++q)
+      if (red_v[q] > best || (red_v[q] == best && red_i[q] < besti)) { best = red_v[q]; besti = red_i[q]; }
+    if (besti == 0x7fffffff) { besti = 0; best = first_s; }
+    const long long o = line * p.T + j;
+    p.mx[o] = best; p.amx[o] = besti; p.flag[o] = (best > p.critical) ? 1 : 0;
+  }
+}
+
+// exp() probe used by the bit-exactness test.
+__global__ void em_exp_probe_kernel(const double* x, double* y, long long n, const ulonglong2* tab) {
+  __shared__ ulonglong2 exp_tab[kExpTableEntries];
+  for (int i = threadIdx.x; i < kExpTableEntries; i += blockDim.x) exp_tab[i] = tab[i];
+  __syncthreads();
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    y[i] = em_exp(x[i], exp_tab);
+}
+
+}  // namespace em
