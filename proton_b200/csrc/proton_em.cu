@@ -1,0 +1,711 @@
+// proton_em.cu — host side of libproton_em.so: the C ABI declared in include/proton_em.h.
+//
+// Owns the context (stream, constant tables, per-length table cache), the plan (a packed ragged batch
+// resident in HBM) and the launch logic that routes each line to a kernel by its length:
+//   N <= 32                      em_eval_small_kernel   (cosine table, one warp per line)
+//   N = 2^p, 64..8192            em_eval_fft_kernel<p, false>   (in-CTA radix-8 DIT FFT)
+//   other N <= 4096              em_eval_fft_kernel<p, true>    (Bluestein, P = 2^p >= 2N-1)
+// There is no CPU fallback: every entry point fails with PROTON_EM_ECUDA when no device is usable.
+#include "../../include/proton_em.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+#include <sys/stat.h>
+#include <cerrno>
+
+#include "em_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_last_error = buf;
+  return code;
+}
+
+#define CU_TRY(expr)                                                                              \
+  do {                                                                                            \
+    cudaError_t e_ = (expr);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(e_ == cudaErrorMemoryAllocation ? PROTON_EM_ENOMEM : PROTON_EM_ECUDA,           \
+                  "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__);    \
+  } while (0)
+
+const unsigned long long kExpTable[2 * em::kExpTableEntries] = {
+#include "exp_table.inc"
+};
+
+constexpr int kMinLog2P = 6, kMaxLog2P = 13;
+constexpr int kMaxPow2N = 1 << kMaxLog2P;          // 8192
+constexpr int kMaxBlueN = (1 << (kMaxLog2P - 1));  // 4096: 2N-1 <= 8192
+
+enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_NONE = 3 };
+
+struct ClassOf { LineClass cls; int log2p; };
+
+ClassOf classify(int N) {
+  if (N <= em::kSmallMaxN) return {CLS_SMALL, 0};
+  if ((N & (N - 1)) == 0) {
+    if (N > kMaxPow2N) return {CLS_NONE, 0};
+    int p = 0;
+    while ((1 << p) < N) ++p;
+    return {CLS_POW2, p};
+  }
+  if (N > kMaxBlueN) return {CLS_NONE, 0};
+  int p = 0;
+  while ((1 << p) < 2 * N - 1) ++p;
+  return {CLS_BLUE, p};
+}
+
+// Bump allocator for the per-length tables (lives as long as the context).
+struct Arena {
+  std::vector<void*> blocks;
+  char* cur = nullptr;
+  size_t left = 0;
+  size_t total = 0;
+  cudaError_t alloc(void** out, size_t bytes) {
+    bytes = (bytes + 255) & ~size_t(255);
+    if (bytes > left) {
+      const size_t blk = std::max(bytes, size_t(32) << 20);
+      void* p = nullptr;
+      cudaError_t e = cudaMalloc(&p, blk);
+      if (e != cudaSuccess) return e;
+      blocks.push_back(p);
+      cur = static_cast<char*>(p);
+      left = blk;
+      total += blk;
+    }
+    *out = cur;
+    cur += bytes;
+    left -= bytes;
+    return cudaSuccess;
+  }
+  void release() {
+    for (void* p : blocks) cudaFree(p);
+    blocks.clear();
+    cur = nullptr;
+    left = 0;
+  }
+};
+
+template <typename T>
+struct DevBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  cudaError_t alloc(size_t count) {
+    free();
+    n = count;
+    if (count == 0) return cudaSuccess;
+    return cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T));
+  }
+  void free() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  size_t bytes() const { return n * sizeof(T); }
+};
+
+}  // namespace
+
+struct proton_em_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  ulonglong2* d_exp = nullptr;
+  em::cplx* d_tw[kMaxLog2P + 1] = {};
+  Arena arena;
+  std::unordered_map<int, em::NTab> tabs;   // per distinct N, device pointers into the arena
+  int64_t launches = 0;
+};
+
+struct proton_em_plan {
+  proton_em_ctx* ctx = nullptr;
+  int64_t L = 0, total_nodes = 0, ntrip = 0, nu = 0;
+  int max_nodes = 0;
+  bool owns_inputs = false;
+  // batch arrays on device (owned when the batch came from the host)
+  const int* d_num_nodes = nullptr;
+  const double* d_a = nullptr;
+  const long long* d_trip_off = nullptr;
+  DevBuf<int> own_num_nodes;
+  DevBuf<double> own_a;
+  DevBuf<long long> own_trip_off;
+  // derived
+  DevBuf<long long> d_node_off;
+  DevBuf<int> d_r_idx, d_r_cnt, d_line_tab;
+  DevBuf<double> d_r_val, d_W;
+  DevBuf<em::NTab> d_tabs;
+  DevBuf<int> d_class_lines;     // concatenated per-class line lists
+  struct ClassList { LineClass cls; int log2p; int offset; int count; };
+  std::vector<ClassList> classes;
+  std::vector<long long> node_off;   // host copy
+  std::vector<int> num_nodes;        // host copy
+};
+
+namespace {
+
+int set_device(proton_em_ctx* ctx) {
+  CU_TRY(cudaSetDevice(ctx->device));
+  return PROTON_EM_OK;
+}
+
+template <int LOG2P, bool BLUE>
+int set_smem_attr() {
+  CU_TRY(cudaFuncSetAttribute(em::em_eval_fft_kernel<LOG2P, BLUE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)em::Cfg<LOG2P, BLUE>::smem_bytes));
+  if (BLUE)
+    CU_TRY(cudaFuncSetAttribute(em::em_tables_kernel<LOG2P, BLUE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(em::padded_len<LOG2P>() * sizeof(em::cplx))));
+  return PROTON_EM_OK;
+}
+
+#define FOR_EACH_LOG2P(M) M(6) M(7) M(8) M(9) M(10) M(11) M(12) M(13)
+
+int init_kernel_attrs() {
+#define M(p)                                                          \
+  { int rc = set_smem_attr<p, false>(); if (rc) return rc; }          \
+  { int rc = set_smem_attr<p, true>(); if (rc) return rc; }
+  FOR_EACH_LOG2P(M)
+#undef M
+  return PROTON_EM_OK;
+}
+
+template <bool BLUE>
+int launch_tables(proton_em_ctx* ctx, int log2p, const em::NTab* d_entries, int count) {
+  em::TableParams tp{d_entries, ctx->d_tw[log2p]};
+  switch (log2p) {
+#define M(p)                                                                                              \
+  case p:                                                                                                 \
+    em::em_tables_kernel<p, BLUE><<<count, em::Cfg<p, BLUE>::NT,                                          \
+                                    BLUE ? em::padded_len<p>() * sizeof(em::cplx) : 0, ctx->stream>>>(tp); \
+    break;
+    FOR_EACH_LOG2P(M)
+#undef M
+    default: return fail(PROTON_EM_EINVAL, "bad log2p %d", log2p);
+  }
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int launch_eval_fft(proton_em_ctx* ctx, bool blue, int log2p, const em::EvalParams& ep, int grid) {
+  switch (log2p) {
+#define M(p)                                                                                                       \
+  case p:                                                                                                          \
+    if (blue) em::em_eval_fft_kernel<p, true><<<grid, em::Cfg<p, true>::NT, em::Cfg<p, true>::smem_bytes, ctx->stream>>>(ep); \
+    else em::em_eval_fft_kernel<p, false><<<grid, em::Cfg<p, false>::NT, em::Cfg<p, false>::smem_bytes, ctx->stream>>>(ep);  \
+    break;
+    FOR_EACH_LOG2P(M)
+#undef M
+    default: return fail(PROTON_EM_EINVAL, "bad log2p %d", log2p);
+  }
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int fft_group(bool blue, int log2p) {
+  switch (log2p) {
+#define M(p) case p: return blue ? em::Cfg<p, true>::G : em::Cfg<p, false>::G;
+    FOR_EACH_LOG2P(M)
+#undef M
+  }
+  return 1;
+}
+
+// lambda_k exactly as the reference computes it (form_analytical_solution, bin/EMtool_analytical@0xc4e8):
+// cos((double)k*pi/(double)N) from the HOST libm — the same libm the reference binary links — doubled,
+// minus 2.0.  A device cos would differ in the last bit often enough to break 1e-9 parity where
+// exp(lambda a t) - 1 cancels.
+void host_lambda(int N, double* out) {
+  const double pi = 3.141592653589793115997963468544185161590576171875;
+  for (int k = 0; k < N; ++k) {
+    volatile double c = std::cos((double)k * pi / (double)N);
+    volatile double c2 = c + c;
+    out[k] = c2 - 2.0;
+  }
+}
+
+// Make sure every distinct N of `lens` has its tables in the context cache.
+int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
+  std::vector<int> fresh;
+  for (int N : distinct)
+    if (ctx->tabs.find(N) == ctx->tabs.end()) fresh.push_back(N);
+  if (fresh.empty()) return PROTON_EM_OK;
+  size_t total = 0;
+  std::vector<size_t> off(fresh.size());
+  for (size_t i = 0; i < fresh.size(); ++i) { off[i] = total; total += (size_t)fresh[i]; }
+  std::vector<double> lam(total);
+  {
+    unsigned nth = std::thread::hardware_concurrency();
+    if (nth == 0) nth = 1;
+    if (total < (size_t)1 << 16) nth = 1;
+    nth = std::min<unsigned>(nth, 64);
+    std::vector<std::thread> pool;
+    std::vector<size_t> order(fresh.size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = i;
+    auto work = [&](unsigned w) {
+      for (size_t i = w; i < fresh.size(); i += nth) host_lambda(fresh[i], lam.data() + off[i]);
+    };
+    for (unsigned w = 1; w < nth; ++w) pool.emplace_back(work, w);
+    work(0);
+    for (auto& t : pool) t.join();
+  }
+  void* d_lam = nullptr;
+  CU_TRY(ctx->arena.alloc(&d_lam, total * sizeof(double)));
+  CU_TRY(cudaMemcpyAsync(d_lam, lam.data(), total * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  // group the new entries by (class, log2p) for the table kernels
+  std::vector<em::NTab> entries(fresh.size());
+  for (size_t i = 0; i < fresh.size(); ++i) {
+    const int N = fresh[i];
+    const ClassOf c = classify(N);
+    em::NTab t{};
+    t.lam = static_cast<const double*>(d_lam) + off[i];
+    t.n = N;
+    t.log2p = (c.cls == CLS_POW2 || c.cls == CLS_BLUE) ? c.log2p : 0;
+    t.bluestein = c.cls == CLS_BLUE;
+    if (c.cls == CLS_POW2 || c.cls == CLS_BLUE) {
+      void* p = nullptr;
+      CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
+      t.pre = static_cast<const em::cplx*>(p);
+    }
+    if (c.cls == CLS_BLUE) {
+      void* p = nullptr;
+      CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
+      t.post = static_cast<const em::cplx*>(p);
+      CU_TRY(ctx->arena.alloc(&p, ((size_t)1 << c.log2p) * sizeof(em::cplx)));
+      t.hhat = static_cast<const em::cplx*>(p);
+    }
+    entries[i] = t;
+  }
+  for (int blue = 0; blue < 2; ++blue) {
+    for (int p = kMinLog2P; p <= kMaxLog2P; ++p) {
+      std::vector<em::NTab> grp;
+      for (const em::NTab& t : entries)
+        if (t.log2p == p && t.bluestein == blue) grp.push_back(t);
+      if (grp.empty()) continue;
+      em::NTab* d_grp = nullptr;
+      CU_TRY(cudaMalloc(reinterpret_cast<void**>(&d_grp), grp.size() * sizeof(em::NTab)));
+      cudaError_t e = cudaMemcpyAsync(d_grp, grp.data(), grp.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, ctx->stream);
+      int rc = PROTON_EM_OK;
+      if (e == cudaSuccess) rc = blue ? launch_tables<true>(ctx, p, d_grp, (int)grp.size())
+                                      : launch_tables<false>(ctx, p, d_grp, (int)grp.size());
+      cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
+      cudaFree(d_grp);
+      if (e != cudaSuccess) CU_TRY(e);
+      if (rc) return rc;
+      CU_TRY(e2);
+    }
+  }
+  CU_TRY(cudaStreamSynchronize(ctx->stream));   // lam upload must finish before `lam` goes away
+  for (const em::NTab& t : entries) ctx->tabs[t.n] = t;
+  return PROTON_EM_OK;
+}
+
+void destroy_plan(proton_em_plan* p) {
+  if (!p) return;
+  p->own_num_nodes.free(); p->own_a.free(); p->own_trip_off.free();
+  p->d_node_off.free(); p->d_r_idx.free(); p->d_r_cnt.free(); p->d_line_tab.free();
+  p->d_r_val.free(); p->d_W.free(); p->d_tabs.free(); p->d_class_lines.free();
+  delete p;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* proton_em_last_error(void) { return g_last_error.c_str(); }
+const char* proton_em_version(void) { return "proton_em 0.1 (sm_100a)"; }
+
+int proton_em_create(proton_em_ctx** out, int device) {
+  if (!out) return fail(PROTON_EM_EINVAL, "proton_em_create: out is NULL");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(PROTON_EM_ECUDA, "no CUDA device available (%s); this library has no CPU path",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (device < 0 || device >= ndev) return fail(PROTON_EM_EINVAL, "device %d out of range [0, %d)", device, ndev);
+  CU_TRY(cudaSetDevice(device));
+  proton_em_ctx* ctx = new proton_em_ctx();
+  ctx->device = device;
+  cudaDeviceProp prop{};
+  CU_TRY(cudaGetDeviceProperties(&prop, device));
+  ctx->sm_count = prop.multiProcessorCount;
+  CU_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_exp), sizeof(kExpTable)));
+  CU_TRY(cudaMemcpy(ctx->d_exp, kExpTable, sizeof(kExpTable), cudaMemcpyHostToDevice));
+  for (int p = kMinLog2P; p <= kMaxLog2P; ++p) {
+    const int P = 1 << p;
+    std::vector<em::cplx> tw(P);
+    const long double two_pi = 6.283185307179586476925286766559005768L;
+    for (int m = 0; m < P; ++m) {
+      const long double ang = two_pi * (long double)m / (long double)P;
+      tw[m].x = (double)cosl(ang);
+      tw[m].y = (double)sinl(ang);
+    }
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tw[p]), P * sizeof(em::cplx)));
+    CU_TRY(cudaMemcpy(ctx->d_tw[p], tw.data(), P * sizeof(em::cplx), cudaMemcpyHostToDevice));
+  }
+  int rc = init_kernel_attrs();
+  if (rc) { proton_em_destroy(ctx); return rc; }
+  *out = ctx;
+  return PROTON_EM_OK;
+}
+
+int proton_em_destroy(proton_em_ctx* ctx) {
+  if (!ctx) return PROTON_EM_OK;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+  if (ctx->d_exp) cudaFree(ctx->d_exp);
+  for (auto* p : ctx->d_tw) if (p) cudaFree(p);
+  ctx->arena.release();
+  delete ctx;
+  return PROTON_EM_OK;
+}
+
+int proton_em_synchronize(proton_em_ctx* ctx) {
+  if (!ctx) return fail(PROTON_EM_EINVAL, "ctx is NULL");
+  CU_TRY(cudaStreamSynchronize(ctx->stream));
+  return PROTON_EM_OK;
+}
+
+void* proton_em_stream(proton_em_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+int64_t proton_em_launch_count(const proton_em_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int proton_em_plan_destroy(proton_em_plan* plan) {
+  if (plan && plan->ctx) { cudaSetDevice(plan->ctx->device); cudaStreamSynchronize(plan->ctx->stream); }
+  destroy_plan(plan);
+  return PROTON_EM_OK;
+}
+int64_t proton_em_plan_total_nodes(const proton_em_plan* plan) { return plan ? plan->total_nodes : 0; }
+int64_t proton_em_plan_num_lines(const proton_em_plan* plan) { return plan ? plan->L : 0; }
+int64_t proton_em_plan_scratch_bytes(const proton_em_plan* p) {
+  if (!p) return 0;
+  return (int64_t)(p->d_node_off.bytes() + p->d_r_idx.bytes() + p->d_r_cnt.bytes() + p->d_line_tab.bytes() +
+                   p->d_r_val.bytes() + p->d_W.bytes() + p->d_tabs.bytes() + p->d_class_lines.bytes());
+}
+
+int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, proton_em_plan** out) {
+  if (!ctx || !b || !out) return fail(PROTON_EM_EINVAL, "proton_em_pack: NULL argument");
+  *out = nullptr;
+  if (location != PROTON_EM_HOST && location != PROTON_EM_DEVICE) return fail(PROTON_EM_EINVAL, "bad location %d", location);
+  const int64_t L = b->num_lines;
+  if (L < 0) return fail(PROTON_EM_EINVAL, "num_lines < 0");
+  if (L > 0 && (!b->num_nodes || !b->a_coeff || !b->trip_off || !b->u_off))
+    return fail(PROTON_EM_EINVAL, "proton_em_pack: NULL batch array");
+  { int rc = set_device(ctx); if (rc) return rc; }
+  proton_em_plan* p = new proton_em_plan();
+  p->ctx = ctx;
+  p->L = L;
+  struct Guard { proton_em_plan* p; ~Guard() { if (p) destroy_plan(p); } } guard{p};
+  if (L == 0) { guard.p = nullptr; *out = p; return PROTON_EM_OK; }
+
+  // ---- host view of the per-line sizes -----------------------------------------------------
+  p->num_nodes.resize(L);
+  std::vector<long long> trip_off(L + 1), u_off(L + 1);
+  if (location == PROTON_EM_HOST) {
+    std::memcpy(p->num_nodes.data(), b->num_nodes, L * sizeof(int));
+    for (int64_t i = 0; i <= L; ++i) { trip_off[i] = b->trip_off[i]; u_off[i] = b->u_off[i]; }
+  } else {
+    CU_TRY(cudaMemcpy(p->num_nodes.data(), b->num_nodes, L * sizeof(int), cudaMemcpyDeviceToHost));
+    CU_TRY(cudaMemcpy(trip_off.data(), b->trip_off, (L + 1) * sizeof(long long), cudaMemcpyDeviceToHost));
+    CU_TRY(cudaMemcpy(u_off.data(), b->u_off, (L + 1) * sizeof(long long), cudaMemcpyDeviceToHost));
+  }
+  for (int64_t i = 0; i < L; ++i) {
+    if (p->num_nodes[i] <= 0) return fail(PROTON_EM_EINVAL, "line %lld: num_nodes = %d", (long long)i, p->num_nodes[i]);
+    if (trip_off[i + 1] < trip_off[i] || u_off[i + 1] < u_off[i])
+      return fail(PROTON_EM_EINVAL, "line %lld: offsets are not non-decreasing", (long long)i);
+    if (trip_off[i + 1] - trip_off[i] > (1 << 20))
+      return fail(PROTON_EM_EINVAL, "line %lld: more than 2^20 triplets", (long long)i);
+  }
+  const long long tbase = trip_off[0], ubase = u_off[0];
+  p->ntrip = trip_off[L] - tbase;
+  p->nu = u_off[L] - ubase;
+  if (p->ntrip > 0 && (!b->trip_row || !b->trip_col || !b->trip_val)) return fail(PROTON_EM_EINVAL, "NULL triplet array");
+  if (p->nu > 0 && !b->curden) return fail(PROTON_EM_EINVAL, "NULL curden array");
+  p->node_off.resize(L + 1);
+  p->node_off[0] = 0;
+  int maxN = 0;
+  for (int64_t i = 0; i < L; ++i) { p->node_off[i + 1] = p->node_off[i] + p->num_nodes[i]; maxN = std::max(maxN, p->num_nodes[i]); }
+  p->total_nodes = p->node_off[L];
+  p->max_nodes = maxN;
+
+  // ---- classes and per-length tables -------------------------------------------------------
+  std::vector<int> distinct(p->num_nodes);
+  std::sort(distinct.begin(), distinct.end());
+  distinct.erase(std::unique(distinct.begin(), distinct.end()), distinct.end());
+  for (int N : distinct)
+    if (classify(N).cls == CLS_NONE)
+      return fail(PROTON_EM_EINVAL, "a line has %d nodes; this build handles N <= %d (any N) and powers of two up to %d",
+                  N, kMaxBlueN, kMaxPow2N);
+  { int rc = ensure_tables(ctx, distinct); if (rc) return rc; }
+  std::unordered_map<int, int> tab_index;
+  std::vector<em::NTab> tabs(distinct.size());
+  for (size_t i = 0; i < distinct.size(); ++i) { tabs[i] = ctx->tabs[distinct[i]]; tab_index[distinct[i]] = (int)i; }
+  std::vector<int> line_tab(L);
+  // class lists: small, pow2[p], blue[p]
+  std::vector<std::vector<int>> lists(1 + 2 * (kMaxLog2P + 1));
+  for (int64_t i = 0; i < L; ++i) {
+    const int N = p->num_nodes[i];
+    line_tab[i] = tab_index[N];
+    const ClassOf c = classify(N);
+    const int slot = c.cls == CLS_SMALL ? 0 : 1 + (c.cls == CLS_BLUE ? kMaxLog2P + 1 : 0) + c.log2p;
+    lists[slot].push_back((int)i);
+  }
+  std::vector<int> class_lines;
+  class_lines.reserve(L);
+  for (size_t s = 0; s < lists.size(); ++s) {
+    if (lists[s].empty()) continue;
+    proton_em_plan::ClassList cl;
+    if (s == 0) { cl.cls = CLS_SMALL; cl.log2p = 0; }
+    else if ((int)s <= kMaxLog2P + 1) { cl.cls = CLS_POW2; cl.log2p = (int)s - 1; }
+    else { cl.cls = CLS_BLUE; cl.log2p = (int)s - 1 - (kMaxLog2P + 1); }
+    // longest lines first inside a class (they are the most expensive items)
+    std::stable_sort(lists[s].begin(), lists[s].end(), [&](int x, int y) { return p->num_nodes[x] > p->num_nodes[y]; });
+    cl.offset = (int)class_lines.size();
+    cl.count = (int)lists[s].size();
+    class_lines.insert(class_lines.end(), lists[s].begin(), lists[s].end());
+    p->classes.push_back(cl);
+  }
+
+  // ---- device copies -----------------------------------------------------------------------
+  cudaStream_t st = ctx->stream;
+  DevBuf<int> tmp_row, tmp_col, tmp_perm;
+  DevBuf<double> tmp_val, tmp_u, tmp_prod;
+  DevBuf<long long> tmp_u_off;
+  DevBuf<int> d_err;
+  struct TmpGuard { DevBuf<int>&a, &b, &c, &e; DevBuf<double>&v, &u, &pr; DevBuf<long long>& uo;
+    ~TmpGuard() { a.free(); b.free(); c.free(); e.free(); v.free(); u.free(); pr.free(); uo.free(); } }
+      tguard{tmp_row, tmp_col, tmp_perm, d_err, tmp_val, tmp_u, tmp_prod, tmp_u_off};
+  const int* d_row; const int* d_col; const double* d_val; const double* d_u; const long long* d_u_off;
+  std::vector<long long> trip_rel, u_rel;
+  if (location == PROTON_EM_HOST) {
+    p->owns_inputs = true;
+    trip_rel.resize(L + 1); u_rel.resize(L + 1);
+    for (int64_t i = 0; i <= L; ++i) { trip_rel[i] = trip_off[i] - tbase; u_rel[i] = u_off[i] - ubase; }
+    CU_TRY(p->own_num_nodes.alloc(L)); CU_TRY(p->own_a.alloc(L)); CU_TRY(p->own_trip_off.alloc(L + 1));
+    CU_TRY(tmp_u_off.alloc(L + 1));
+    CU_TRY(tmp_row.alloc(p->ntrip)); CU_TRY(tmp_col.alloc(p->ntrip)); CU_TRY(tmp_val.alloc(p->ntrip)); CU_TRY(tmp_u.alloc(p->nu));
+    CU_TRY(cudaMemcpyAsync(p->own_num_nodes.p, b->num_nodes, L * sizeof(int), cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaMemcpyAsync(p->own_a.p, b->a_coeff, L * sizeof(double), cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaMemcpyAsync(p->own_trip_off.p, trip_rel.data(), (L + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    CU_TRY(cudaMemcpyAsync(tmp_u_off.p, u_rel.data(), (L + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    if (p->ntrip) {
+      CU_TRY(cudaMemcpyAsync(tmp_row.p, b->trip_row + tbase, p->ntrip * sizeof(int), cudaMemcpyHostToDevice, st));
+      CU_TRY(cudaMemcpyAsync(tmp_col.p, b->trip_col + tbase, p->ntrip * sizeof(int), cudaMemcpyHostToDevice, st));
+      CU_TRY(cudaMemcpyAsync(tmp_val.p, b->trip_val + tbase, p->ntrip * sizeof(double), cudaMemcpyHostToDevice, st));
+    }
+    if (p->nu) CU_TRY(cudaMemcpyAsync(tmp_u.p, b->curden + ubase, p->nu * sizeof(double), cudaMemcpyHostToDevice, st));
+    p->d_num_nodes = p->own_num_nodes.p; p->d_a = p->own_a.p; p->d_trip_off = p->own_trip_off.p;
+    d_row = tmp_row.p; d_col = tmp_col.p; d_val = tmp_val.p; d_u = tmp_u.p; d_u_off = tmp_u_off.p;
+  } else {
+    // device-resident batch: num_nodes / a_coeff / trip_off stay referenced by the plan (caller keeps them alive)
+    p->d_num_nodes = b->num_nodes; p->d_a = b->a_coeff;
+    if (tbase == 0) p->d_trip_off = reinterpret_cast<const long long*>(b->trip_off);
+    else {
+      trip_rel.resize(L + 1);
+      for (int64_t i = 0; i <= L; ++i) trip_rel[i] = trip_off[i] - tbase;
+      CU_TRY(p->own_trip_off.alloc(L + 1));
+      CU_TRY(cudaMemcpyAsync(p->own_trip_off.p, trip_rel.data(), (L + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+      p->d_trip_off = p->own_trip_off.p;
+    }
+    d_row = b->trip_row + tbase; d_col = b->trip_col + tbase; d_val = b->trip_val + tbase;
+    if (ubase == 0) { d_u_off = reinterpret_cast<const long long*>(b->u_off); d_u = b->curden; }
+    else {
+      u_rel.resize(L + 1);
+      for (int64_t i = 0; i <= L; ++i) u_rel[i] = u_off[i] - ubase;
+      CU_TRY(tmp_u_off.alloc(L + 1));
+      CU_TRY(cudaMemcpyAsync(tmp_u_off.p, u_rel.data(), (L + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+      d_u_off = tmp_u_off.p; d_u = b->curden + ubase;
+    }
+  }
+  CU_TRY(p->d_node_off.alloc(L + 1)); CU_TRY(p->d_line_tab.alloc(L)); CU_TRY(p->d_tabs.alloc(tabs.size()));
+  CU_TRY(p->d_class_lines.alloc(class_lines.size()));
+  CU_TRY(p->d_r_idx.alloc(std::max<int64_t>(p->ntrip, 1))); CU_TRY(p->d_r_val.alloc(std::max<int64_t>(p->ntrip, 1)));
+  CU_TRY(p->d_r_cnt.alloc(L)); CU_TRY(p->d_W.alloc(p->total_nodes));
+  CU_TRY(tmp_perm.alloc(std::max<int64_t>(p->ntrip, 1))); CU_TRY(tmp_prod.alloc(std::max<int64_t>(p->ntrip, 1)));
+  CU_TRY(d_err.alloc(1));
+  CU_TRY(cudaMemcpyAsync(p->d_node_off.p, p->node_off.data(), (L + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(p->d_line_tab.p, line_tab.data(), L * sizeof(int), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(p->d_tabs.p, tabs.data(), tabs.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemcpyAsync(p->d_class_lines.p, class_lines.data(), class_lines.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  CU_TRY(cudaMemsetAsync(d_err.p, 0, sizeof(int), st));
+
+  // ---- (a) packing kernel, (b) forward DCT kernel ------------------------------------------
+  em::PackParams pp{L, p->d_num_nodes, p->d_trip_off, d_row, d_col, d_val, d_u_off, d_u,
+                    tmp_perm.p, tmp_prod.p, p->d_r_idx.p, p->d_r_val.p, p->d_r_cnt.p, d_err.p};
+  const int pack_grid = (int)std::min<int64_t>(L, (int64_t)ctx->sm_count * 16);
+  em::em_pack_kernel<<<pack_grid, 128, 0, st>>>(pp);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  em::ForwardParams fp{L, p->total_nodes, p->d_num_nodes, p->d_a, p->d_node_off.p, p->d_trip_off,
+                       p->d_r_idx.p, p->d_r_val.p, p->d_r_cnt.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p};
+  const int fwd_grid = (int)std::min<int64_t>((p->total_nodes + 255) / 256, (int64_t)ctx->sm_count * 32);
+  em::em_forward_kernel<<<fwd_grid, 256, 0, st>>>(fp);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  int err = 0;
+  CU_TRY(cudaMemcpyAsync(&err, d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  if (err != 0)
+    return fail(PROTON_EM_EINVAL, "line %d: a B triplet has a row outside [0, num_nodes) or a column outside [0, #curden)", err - 1);
+  guard.p = nullptr;
+  *out = p;
+  return PROTON_EM_OK;
+}
+
+static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proton_em_opts* opts,
+                       double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag) {
+  proton_em_ctx* ctx = p->ctx;
+  const double critical = opts ? opts->critical_stress : NAN;
+  const int alg = opts ? opts->algorithm : PROTON_EM_ALG_AUTO;
+  if (alg == PROTON_EM_ALG_DIRECT) {
+    if ((long long)p->L * T > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "direct algorithm: L*T too large");
+    em::DirectParams dp{p->L, T, p->d_num_nodes, p->d_a, p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p,
+                        d_ts, ctx->d_exp, d_stress, d_mx, d_amx, d_flag, critical};
+    em::em_eval_direct_kernel<<<(unsigned)(p->L * T), 256, 0, ctx->stream>>>(dp);
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
+    return PROTON_EM_OK;
+  }
+  if (alg != PROTON_EM_ALG_AUTO) return fail(PROTON_EM_EINVAL, "unknown algorithm %d", alg);
+  const long long target_items = (long long)ctx->sm_count * 12;
+  for (const auto& cl : p->classes) {
+    if (cl.cls == CLS_SMALL) {
+      int chunks = (int)std::min<long long>(T, std::max<long long>(1, target_items * 4 / cl.count));
+      int tpc = (T + chunks - 1) / chunks;
+      chunks = (T + tpc - 1) / tpc;
+      em::SmallParams sp{p->d_class_lines.p + cl.offset, cl.count, chunks, tpc, T, p->d_num_nodes, p->d_a,
+                         p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_exp,
+                         d_stress, d_mx, d_amx, d_flag, critical};
+      const long long items = (long long)cl.count * chunks;
+      em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, ctx->stream>>>(sp);
+      ctx->launches++;
+      CU_TRY(cudaGetLastError());
+      continue;
+    }
+    const bool blue = cl.cls == CLS_BLUE;
+    const int G = fft_group(blue, cl.log2p);
+    const int npairs = (T + 1) / 2;
+    const int max_chunks = (npairs + G - 1) / G;
+    int chunks = (int)std::min<long long>(max_chunks, std::max<long long>(1, (target_items + cl.count - 1) / cl.count));
+    int ppc = (npairs + chunks - 1) / chunks;
+    ppc = ((ppc + G - 1) / G) * G;
+    chunks = (npairs + ppc - 1) / ppc;
+    em::EvalParams ep{p->d_class_lines.p + cl.offset, cl.count, chunks, ppc, T, p->d_num_nodes, p->d_a,
+                      p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_tw[cl.log2p], ctx->d_exp,
+                      d_stress, d_mx, d_amx, d_flag, critical};
+    const long long grid = (long long)cl.count * chunks;
+    if (grid > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many work items");
+    int rc = launch_eval_fft(ctx, blue, cl.log2p, ep, (int)grid);
+    if (rc) return rc;
+  }
+  return PROTON_EM_OK;
+}
+
+int proton_em_eval(proton_em_plan* p, const double* ts, int32_t T, const proton_em_opts* opts,
+                   const proton_em_result* res, int location) {
+  if (!p || !res) return fail(PROTON_EM_EINVAL, "proton_em_eval: NULL argument");
+  if (T < 0) return fail(PROTON_EM_EINVAL, "T < 0");
+  if (T == 0 || p->L == 0) return PROTON_EM_OK;
+  if (!ts || !res->max_stress || !res->argmax || !res->flag)
+    return fail(PROTON_EM_EINVAL, "proton_em_eval: ts, max_stress, argmax and flag are required");
+  proton_em_ctx* ctx = p->ctx;
+  { int rc = set_device(ctx); if (rc) return rc; }
+  if (location == PROTON_EM_DEVICE)
+    return eval_device(p, ts, T, opts, res->stress, res->max_stress, res->argmax, res->flag);
+  if (location != PROTON_EM_HOST) return fail(PROTON_EM_EINVAL, "bad location %d", location);
+  const size_t LT = (size_t)p->L * T;
+  DevBuf<double> d_ts, d_mx, d_stress;
+  DevBuf<int> d_amx;
+  DevBuf<unsigned char> d_flag;
+  struct G2 { DevBuf<double>&a, &b, &c; DevBuf<int>& d; DevBuf<unsigned char>& e;
+    ~G2() { a.free(); b.free(); c.free(); d.free(); e.free(); } } g2{d_ts, d_mx, d_stress, d_amx, d_flag};
+  CU_TRY(d_ts.alloc(T)); CU_TRY(d_mx.alloc(LT)); CU_TRY(d_amx.alloc(LT)); CU_TRY(d_flag.alloc(LT));
+  if (res->stress) CU_TRY(d_stress.alloc((size_t)p->total_nodes * T));
+  CU_TRY(cudaMemcpyAsync(d_ts.p, ts, T * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  int rc = eval_device(p, d_ts.p, T, opts, res->stress ? d_stress.p : nullptr, d_mx.p, d_amx.p, d_flag.p);
+  if (rc) { cudaStreamSynchronize(ctx->stream); return rc; }
+  if (res->stress)
+    CU_TRY(cudaMemcpyAsync(res->stress, d_stress.p, d_stress.bytes(), cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(cudaMemcpyAsync(res->max_stress, d_mx.p, d_mx.bytes(), cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(cudaMemcpyAsync(res->argmax, d_amx.p, d_amx.bytes(), cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(cudaMemcpyAsync(res->flag, d_flag.p, d_flag.bytes(), cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(cudaStreamSynchronize(ctx->stream));
+  return PROTON_EM_OK;
+}
+
+int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const double* ts, int32_t T,
+                           const proton_em_opts* opts, const proton_em_result* res, int64_t max_device_bytes) {
+  if (!ctx || !b || !res) return fail(PROTON_EM_EINVAL, "proton_em_analyze_host: NULL argument");
+  if (T <= 0 || b->num_lines <= 0) return PROTON_EM_OK;
+  if (max_device_bytes <= 0) max_device_bytes = (int64_t)16 << 30;
+  const int64_t L = b->num_lines;
+  int64_t l0 = 0;
+  int64_t node_base = 0;
+  while (l0 < L) {
+    int64_t l1 = l0, nodes = 0;
+    while (l1 < L) {
+      const int64_t n = b->num_nodes[l1];
+      if (l1 > l0 && res->stress && (nodes + n) * (int64_t)T * 8 > max_device_bytes) break;
+      nodes += n;
+      ++l1;
+    }
+    proton_em_batch sub = *b;
+    sub.num_lines = l1 - l0;
+    sub.num_nodes = b->num_nodes + l0;
+    sub.a_coeff = b->a_coeff + l0;
+    sub.trip_off = b->trip_off + l0;
+    sub.u_off = b->u_off + l0;
+    proton_em_plan* plan = nullptr;
+    int rc = proton_em_pack(ctx, &sub, PROTON_EM_HOST, &plan);
+    if (rc) return rc;
+    proton_em_result r2;
+    r2.stress = res->stress ? res->stress + node_base * T : nullptr;
+    r2.max_stress = res->max_stress + l0 * T;
+    r2.argmax = res->argmax + l0 * T;
+    r2.flag = res->flag + l0 * T;
+    rc = proton_em_eval(plan, ts, T, opts, &r2, PROTON_EM_HOST);
+    destroy_plan(plan);
+    if (rc) return rc;
+    node_base += nodes;
+    l0 = l1;
+  }
+  return PROTON_EM_OK;
+}
+
+int proton_em_debug_exp(proton_em_ctx* ctx, const double* x, double* y, int64_t n) {
+  if (!ctx || !x || !y || n < 0) return fail(PROTON_EM_EINVAL, "proton_em_debug_exp: bad argument");
+  if (n == 0) return PROTON_EM_OK;
+  { int rc = set_device(ctx); if (rc) return rc; }
+  DevBuf<double> dx, dy;
+  struct G3 { DevBuf<double>&a, &b; ~G3() { a.free(); b.free(); } } g3{dx, dy};
+  CU_TRY(dx.alloc(n)); CU_TRY(dy.alloc(n));
+  CU_TRY(cudaMemcpyAsync(dx.p, x, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  em::em_exp_probe_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(dx.p, dy.p, n, ctx->d_exp);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  CU_TRY(cudaMemcpyAsync(y, dy.p, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU_TRY(cudaStreamSynchronize(ctx->stream));
+  return PROTON_EM_OK;
+}
+
+}  // extern "C"
