@@ -1,0 +1,84 @@
+"""ctypes binding of libproton_em.so (include/proton_em.h).  There is no fallback: if the CUDA library is
+missing or no GPU is usable, every call fails loudly."""
+from __future__ import annotations
+
+import ctypes
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libproton_em.so"
+
+OK, EINVAL, ENOMEM, ECUDA, EIO = 0, -1, -2, -3, -4
+HOST, DEVICE = 0, 1
+ALG_AUTO, ALG_DIRECT = 0, 1
+
+c_i32p = ctypes.POINTER(ctypes.c_int32)
+c_i64p = ctypes.POINTER(ctypes.c_int64)
+c_dp = ctypes.POINTER(ctypes.c_double)
+c_u8p = ctypes.POINTER(ctypes.c_uint8)
+
+
+class Batch(ctypes.Structure):
+    _fields_ = [("num_lines", ctypes.c_int64), ("num_nodes", ctypes.c_void_p), ("a_coeff", ctypes.c_void_p),
+                ("trip_off", ctypes.c_void_p), ("trip_row", ctypes.c_void_p), ("trip_col", ctypes.c_void_p),
+                ("trip_val", ctypes.c_void_p), ("u_off", ctypes.c_void_p), ("curden", ctypes.c_void_p)]
+
+
+class Opts(ctypes.Structure):
+    _fields_ = [("critical_stress", ctypes.c_double), ("algorithm", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
+class Result(ctypes.Structure):
+    _fields_ = [("stress", ctypes.c_void_p), ("max_stress", ctypes.c_void_p), ("argmax", ctypes.c_void_p),
+                ("flag", ctypes.c_void_p)]
+
+
+class ProtonEmError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"proton_em error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+_lib = None
+
+EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "proton_em_version", "proton_em_pack",
+           "proton_em_plan_destroy", "proton_em_plan_total_nodes", "proton_em_plan_num_lines",
+           "proton_em_plan_scratch_bytes", "proton_em_eval", "proton_em_synchronize", "proton_em_stream",
+           "proton_em_launch_count", "proton_em_analyze_host", "proton_em_run_cfg", "proton_em_debug_exp"]
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise ProtonEmError(ECUDA, f"{LIB_PATH} is not built (run `python -m proton_b200.build`); "
+                                   "there is no CPU fallback")
+    lib = ctypes.CDLL(str(LIB_PATH))
+    vp = ctypes.c_void_p
+    lib.proton_em_create.argtypes = [ctypes.POINTER(vp), ctypes.c_int]
+    lib.proton_em_destroy.argtypes = [vp]
+    lib.proton_em_last_error.restype = ctypes.c_char_p
+    lib.proton_em_version.restype = ctypes.c_char_p
+    lib.proton_em_pack.argtypes = [vp, ctypes.POINTER(Batch), ctypes.c_int, ctypes.POINTER(vp)]
+    lib.proton_em_plan_destroy.argtypes = [vp]
+    for f in (lib.proton_em_plan_total_nodes, lib.proton_em_plan_num_lines, lib.proton_em_plan_scratch_bytes,
+              lib.proton_em_launch_count):
+        f.argtypes = [vp]
+        f.restype = ctypes.c_int64
+    lib.proton_em_eval.argtypes = [vp, vp, ctypes.c_int32, ctypes.POINTER(Opts), ctypes.POINTER(Result), ctypes.c_int]
+    lib.proton_em_synchronize.argtypes = [vp]
+    lib.proton_em_stream.argtypes = [vp]
+    lib.proton_em_stream.restype = vp
+    lib.proton_em_analyze_host.argtypes = [vp, ctypes.POINTER(Batch), vp, ctypes.c_int32, ctypes.POINTER(Opts),
+                                           ctypes.POINTER(Result), ctypes.c_int64]
+    lib.proton_em_run_cfg.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t]
+    lib.proton_em_debug_exp.argtypes = [vp, vp, vp, ctypes.c_int64]
+    _lib = lib
+    return lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise ProtonEmError(rc, load().proton_em_last_error().decode(errors="replace"))

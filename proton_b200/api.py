@@ -1,0 +1,243 @@
+"""Python front-end of the batched line-analysis library (libproton_em.so).
+
+`LineBatch` is the ragged batch the C ABI consumes (include/proton_em.h: proton_em_batch) — per line the
+contents of the reference's `analytical.cfg`, `B.csv` and `curden.csv`.  `Context.pack` uploads it and runs the
+packing and forward-DCT kernels; `Plan.eval` evaluates it at any number of timestamps.  Host (numpy) and
+device (torch CUDA tensor) entry points are separate so nothing is copied behind the caller's back.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Iterable, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import ALG_AUTO, ALG_DIRECT, DEVICE, HOST, Batch, Opts, ProtonEmError, Result, check
+
+
+@dataclass
+class LineBatch:
+    num_nodes: np.ndarray   # int32 [L]
+    a_coeff: np.ndarray     # float64 [L]
+    trip_off: np.ndarray    # int64 [L+1]
+    trip_row: np.ndarray    # int32
+    trip_col: np.ndarray    # int32
+    trip_val: np.ndarray    # float64
+    u_off: np.ndarray       # int64 [L+1]
+    curden: np.ndarray      # float64
+    names: Optional[list] = None
+
+    def __post_init__(self):
+        self.num_nodes = np.ascontiguousarray(self.num_nodes, dtype=np.int32)
+        self.a_coeff = np.ascontiguousarray(self.a_coeff, dtype=np.float64)
+        self.trip_off = np.ascontiguousarray(self.trip_off, dtype=np.int64)
+        self.trip_row = np.ascontiguousarray(self.trip_row, dtype=np.int32)
+        self.trip_col = np.ascontiguousarray(self.trip_col, dtype=np.int32)
+        self.trip_val = np.ascontiguousarray(self.trip_val, dtype=np.float64)
+        self.u_off = np.ascontiguousarray(self.u_off, dtype=np.int64)
+        self.curden = np.ascontiguousarray(self.curden, dtype=np.float64)
+        L = len(self.num_nodes)
+        if len(self.a_coeff) != L or len(self.trip_off) != L + 1 or len(self.u_off) != L + 1:
+            raise ValueError("LineBatch: inconsistent array lengths")
+
+    @property
+    def num_lines(self) -> int:
+        return len(self.num_nodes)
+
+    @property
+    def node_off(self) -> np.ndarray:
+        off = np.zeros(self.num_lines + 1, dtype=np.int64)
+        np.cumsum(self.num_nodes, out=off[1:])
+        return off
+
+    @property
+    def total_nodes(self) -> int:
+        return int(self.num_nodes.astype(np.int64).sum())
+
+    @staticmethod
+    def from_lines(lines: Iterable) -> "LineBatch":
+        """From objects with num_nodes, a_coeff, rows, cols, vals, curden (proton_b200.formulation.LineInputs)."""
+        lines = list(lines)
+        trip_off = np.zeros(len(lines) + 1, dtype=np.int64)
+        u_off = np.zeros(len(lines) + 1, dtype=np.int64)
+        for i, li in enumerate(lines):
+            trip_off[i + 1] = trip_off[i] + len(li.rows)
+            u_off[i + 1] = u_off[i] + len(li.curden)
+        cat = lambda xs, dt: (np.concatenate(xs).astype(dt) if xs else np.zeros(0, dt))
+        return LineBatch(num_nodes=[li.num_nodes for li in lines], a_coeff=[li.a_coeff for li in lines],
+                         trip_off=trip_off, trip_row=cat([np.asarray(li.rows) for li in lines], np.int32),
+                         trip_col=cat([np.asarray(li.cols) for li in lines], np.int32),
+                         trip_val=cat([np.asarray(li.vals) for li in lines], np.float64), u_off=u_off,
+                         curden=cat([np.asarray(li.curden) for li in lines], np.float64),
+                         names=[getattr(li, "name", str(i)) for i, li in enumerate(lines)])
+
+    def subset(self, idx: Sequence[int]) -> "LineBatch":
+        idx = np.asarray(idx, dtype=np.int64)
+        tl = self.trip_off[idx + 1] - self.trip_off[idx]
+        ul = self.u_off[idx + 1] - self.u_off[idx]
+        trip_off = np.concatenate([[0], np.cumsum(tl)])
+        u_off = np.concatenate([[0], np.cumsum(ul)])
+        tsel = np.concatenate([np.arange(self.trip_off[i], self.trip_off[i + 1]) for i in idx]) if len(idx) else np.zeros(0, np.int64)
+        usel = np.concatenate([np.arange(self.u_off[i], self.u_off[i + 1]) for i in idx]) if len(idx) else np.zeros(0, np.int64)
+        return LineBatch(self.num_nodes[idx], self.a_coeff[idx], trip_off, self.trip_row[tsel], self.trip_col[tsel],
+                         self.trip_val[tsel], u_off, self.curden[usel],
+                         names=[self.names[i] for i in idx] if self.names else None)
+
+    def _as_c(self) -> Batch:
+        p = lambda a: a.ctypes.data if a.size else None
+        return Batch(self.num_lines, p(self.num_nodes), p(self.a_coeff), self.trip_off.ctypes.data, p(self.trip_row),
+                     p(self.trip_col), p(self.trip_val), self.u_off.ctypes.data, p(self.curden))
+
+
+@dataclass
+class EvalResult:
+    stress: Optional[np.ndarray]   # flat; line l at node_off[l]*T, [T][N_l]
+    max_stress: np.ndarray         # [L, T]
+    argmax: np.ndarray             # [L, T]
+    flag: np.ndarray               # [L, T] uint8
+    node_off: np.ndarray
+    T: int
+
+    def line(self, l: int) -> np.ndarray:
+        a, b = int(self.node_off[l]), int(self.node_off[l + 1])
+        return self.stress[a * self.T:b * self.T].reshape(self.T, b - a)
+
+
+def _opts(critical, algorithm) -> Opts:
+    return Opts(float("nan") if critical is None else float(critical), int(algorithm), 0)
+
+
+class Context:
+    """One per (process, GPU)."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _lib.load()
+        self._h = ctypes.c_void_p()
+        check(self._lib.proton_em_create(ctypes.byref(self._h), int(device)))
+        self.device = int(device)
+
+    def close(self):
+        if self._h:
+            self._lib.proton_em_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.proton_em_launch_count(self._h))
+
+    @property
+    def stream(self) -> int:
+        return int(self._lib.proton_em_stream(self._h) or 0)
+
+    def synchronize(self):
+        check(self._lib.proton_em_synchronize(self._h))
+
+    def pack(self, batch: LineBatch) -> "Plan":
+        h = ctypes.c_void_p()
+        cb = batch._as_c()
+        check(self._lib.proton_em_pack(self._h, ctypes.byref(cb), HOST, ctypes.byref(h)))
+        return Plan(self, h, batch.node_off, keep=None)
+
+    def pack_device(self, num_nodes, a_coeff, trip_off, trip_row, trip_col, trip_val, u_off, curden) -> "Plan":
+        """All arguments are torch CUDA tensors (int32 / float64 / int64 as in proton_em_batch); the plan keeps
+        references to them because the kernels read num_nodes / a_coeff / trip_off in place."""
+        keep = (num_nodes, a_coeff, trip_off, trip_row, trip_col, trip_val, u_off, curden)
+        for t in keep:
+            if not t.is_cuda or not t.is_contiguous():
+                raise ValueError("pack_device needs contiguous CUDA tensors")
+        cb = Batch(int(num_nodes.numel()), num_nodes.data_ptr(), a_coeff.data_ptr(), trip_off.data_ptr(),
+                   trip_row.data_ptr(), trip_col.data_ptr(), trip_val.data_ptr(), u_off.data_ptr(), curden.data_ptr())
+        h = ctypes.c_void_p()
+        check(self._lib.proton_em_pack(self._h, ctypes.byref(cb), DEVICE, ctypes.byref(h)))
+        node_off = np.zeros(int(num_nodes.numel()) + 1, dtype=np.int64)
+        np.cumsum(num_nodes.cpu().numpy(), out=node_off[1:])
+        return Plan(self, h, node_off, keep=keep)
+
+    def analyze_host(self, batch: LineBatch, ts, critical=None, want_stress=True, algorithm=ALG_AUTO,
+                     max_device_bytes: int = 0, out: Optional[EvalResult] = None) -> EvalResult:
+        """pack + eval + copy back in one C call (the end-to-end path).  `out` may hold preallocated (e.g.
+        pinned) arrays to write into."""
+        ts = np.ascontiguousarray(np.atleast_1d(ts), dtype=np.float64)
+        T, L = len(ts), batch.num_lines
+        if out is None:
+            out = EvalResult(np.empty(batch.total_nodes * T) if want_stress else None, np.empty((L, T)),
+                             np.empty((L, T), np.int32), np.empty((L, T), np.uint8), batch.node_off, T)
+        res = Result(out.stress.ctypes.data if out.stress is not None else None, out.max_stress.ctypes.data,
+                     out.argmax.ctypes.data, out.flag.ctypes.data)
+        cb = batch._as_c()
+        o = _opts(critical, algorithm)
+        check(self._lib.proton_em_analyze_host(self._h, ctypes.byref(cb), ts.ctypes.data, T, ctypes.byref(o),
+                                               ctypes.byref(res), int(max_device_bytes)))
+        return out
+
+    def debug_exp(self, x) -> np.ndarray:
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.empty_like(x)
+        check(self._lib.proton_em_debug_exp(self._h, x.ctypes.data, y.ctypes.data, x.size))
+        return y
+
+    def run_cfg(self, cfg_path: str):
+        """The reference process for one analytical.cfg -> (return code, stdout text of the reference)."""
+        buf = ctypes.create_string_buffer(2048)
+        rc = self._lib.proton_em_run_cfg(self._h, str(cfg_path).encode(), buf, len(buf))
+        return rc, buf.value.decode(errors="replace")
+
+
+class Plan:
+    def __init__(self, ctx: Context, handle, node_off: np.ndarray, keep):
+        self.ctx = ctx
+        self._h = handle
+        self.node_off = node_off
+        self._keep = keep
+
+    @property
+    def num_lines(self) -> int:
+        return len(self.node_off) - 1
+
+    @property
+    def total_nodes(self) -> int:
+        return int(self.node_off[-1])
+
+    @property
+    def scratch_bytes(self) -> int:
+        return int(self.ctx._lib.proton_em_plan_scratch_bytes(self._h))
+
+    def close(self):
+        if self._h:
+            self.ctx._lib.proton_em_plan_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def eval(self, ts, critical=None, want_stress=True, algorithm=ALG_AUTO) -> EvalResult:
+        """Host call: timestamps in, numpy results out (copies and synchronises)."""
+        ts = np.ascontiguousarray(np.atleast_1d(ts), dtype=np.float64)
+        T, L = len(ts), self.num_lines
+        out = EvalResult(np.empty(self.total_nodes * T) if want_stress else None, np.empty((L, T)),
+                         np.empty((L, T), np.int32), np.empty((L, T), np.uint8), self.node_off, T)
+        res = Result(out.stress.ctypes.data if want_stress else None, out.max_stress.ctypes.data,
+                     out.argmax.ctypes.data, out.flag.ctypes.data)
+        o = _opts(critical, algorithm)
+        check(self.ctx._lib.proton_em_eval(self._h, ts.ctypes.data, T, ctypes.byref(o), ctypes.byref(res), HOST))
+        return out
+
+    def eval_device(self, ts, stress, max_stress, argmax, flag, critical=None, algorithm=ALG_AUTO) -> None:
+        """Device call: all arguments are torch CUDA tensors (stress may be None); work is queued on the
+        context's stream and NOT synchronised."""
+        T = int(ts.numel())
+        res = Result(stress.data_ptr() if stress is not None else None, max_stress.data_ptr(), argmax.data_ptr(),
+                     flag.data_ptr())
+        o = _opts(critical, algorithm)
+        check(self.ctx._lib.proton_em_eval(self._h, ts.data_ptr(), T, ctypes.byref(o), ctypes.byref(res), DEVICE))

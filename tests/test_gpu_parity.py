@@ -1,0 +1,209 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the CPU oracle and the
+reference-binary goldens.  Tolerance: norm-wise 1e-9 per (line, timestamp) as BASELINE.json's north_star
+states; N == 1 lines must be exact."""
+import numpy as np
+import pytest
+
+from gpu_common import compare, oracle_batch, self_consistent, synth_batch, synth_line
+
+pytestmark = pytest.mark.gpu
+
+TS100 = np.logspace(6, np.log10(6.38e8), 100)
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from proton_b200.api import Context
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def test_device_exp_equals_host_libm_bit_for_bit(ctx, oracle):
+    rng = np.random.default_rng(1)
+    xs = np.concatenate([
+        rng.uniform(-50, 0, 2_000_000), -np.exp(rng.uniform(np.log(1e-20), np.log(1.0), 1_000_000)),
+        rng.uniform(-800, -500, 200_000), rng.uniform(-1100, -700, 100_000), rng.uniform(0, 50, 200_000),
+        rng.uniform(500, 720, 100_000),
+        np.array([0.0, -0.0, 1e-300, -1e-300, -2.0 ** -54, -2.0 ** -53, -745.2, -746.0, -1e4, 1e4, np.inf, -np.inf,
+                  709.7, 710.0, -708.4, -512.0, -511.999, -1023.9, -1024.0])])
+    got = ctx.debug_exp(xs)
+    want = oracle.libm_exp(xs)
+    same = got.view(np.uint64) == want.view(np.uint64)
+    assert same.all(), f"{(~same).sum()} of {len(xs)} differ, first x={xs[~same][:5]}"
+    assert np.isnan(ctx.debug_exp(np.array([np.nan]))[0])
+
+
+def _golden_batch(g, idx):
+    from proton_b200.api import LineBatch
+    tl = [g["trip_off"][i + 1] - g["trip_off"][i] for i in idx]
+    ul = [g["u_off"][i + 1] - g["u_off"][i] for i in idx]
+    cat = lambda key, off: np.concatenate([g[key][g[off][i]:g[off][i + 1]] for i in idx])
+    return LineBatch(g["num_nodes"][idx], g["a_coeff"][idx], np.concatenate([[0], np.cumsum(tl)]), cat("rows", "trip_off"),
+                     cat("cols", "trip_off"), cat("vals", "trip_off"), np.concatenate([[0], np.cumsum(ul)]),
+                     cat("curden", "u_off"))
+
+
+def test_reference_binary_goldens(ctx, binary_golden):
+    g = binary_golden
+    worst = 0.0
+    for t in np.unique(g["t"]):
+        idx = np.nonzero(g["t"] == t)[0]
+        batch = _golden_batch(g, idx)
+        got = ctx.analyze_host(batch, [t], critical=40e6)
+        for k, i in enumerate(idx):
+            want = g["stress"][g["stress_off"][i]:g["stress_off"][i + 1]]
+            have = got.line(k)[0]
+            scale = np.abs(want).max()
+            if len(want) == 1:
+                assert have[0] == want[0], g["tag"][i]
+                continue
+            err = np.abs(have - want).max() / scale
+            assert err <= 1e-9, (g["tag"][i], err)
+            worst = max(worst, err)
+            assert abs(got.max_stress[k, 0] - want.max()) <= 1e-9 * scale
+    print(f"worst norm-wise error vs reference binary goldens: {worst:.3e}")
+    assert worst < 1e-11
+
+
+SIZES_ALL_CLASSES = [1, 2, 3, 5, 8, 16, 17, 31, 32, 33, 34, 47, 63, 64, 65, 100, 127, 128, 129, 200, 255, 256, 257, 400,
+                     511, 512, 513, 777, 1000, 1023, 1024, 1025, 1500, 2047, 2048, 2049, 3000, 4095, 4096, 8192]
+
+
+@pytest.mark.parametrize("T", [1, 2, 7, 100])
+def test_all_length_classes_against_oracle(ctx, oracle, T):
+    rng = np.random.default_rng(100 + T)
+    batch = synth_batch(rng, SIZES_ALL_CLASSES)
+    ts = TS100[:T] if T < 100 else TS100
+    if T == 7:
+        ts = np.array([1e6, 3e6, 1e7, 5e7, 1e8, 3e8, 6.38e8])
+    got = ctx.analyze_host(batch, ts, critical=40e6)
+    ws, wm, wa = oracle_batch(oracle, batch, ts)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    self_consistent(batch, ts, got, 40e6)
+    print(f"T={T}: worst norm-wise error {worst:.3e}")
+
+
+def test_random_ragged_batch_against_oracle(ctx, oracle):
+    rng = np.random.default_rng(7)
+    sizes = np.exp(rng.uniform(np.log(1), np.log(4096), 300)).astype(int)
+    batch = synth_batch(rng, sizes)
+    ts = np.logspace(6, np.log10(6.38e8), 16)
+    plan = ctx.pack(batch)
+    got = plan.eval(ts, critical=1e8)
+    ws, wm, wa = oracle_batch(oracle, batch, ts)
+    compare(batch, ts, got, ws, wm, wa, critical=1e8)
+    self_consistent(batch, ts, got, 1e8)
+    # the plan can be evaluated again at other timestamps (and in reduce-only mode)
+    got2 = plan.eval(ts[3:5], critical=1e8, want_stress=False)
+    assert got2.stress is None
+    assert np.array_equal(got2.max_stress, got.max_stress[:, 3:5])
+    assert np.array_equal(got2.argmax, got.argmax[:, 3:5])
+    plan.close()
+
+
+def test_direct_kernel_cross_check(ctx, oracle):
+    from proton_b200.api import ALG_DIRECT
+    rng = np.random.default_rng(11)
+    batch = synth_batch(rng, [1, 4, 33, 100, 256, 300, 700])
+    ts = np.array([1e6, 1e8, 6.38e8])
+    plan = ctx.pack(batch)
+    fast = plan.eval(ts, critical=0.0)
+    slow = plan.eval(ts, critical=0.0, algorithm=ALG_DIRECT)
+    off = batch.node_off
+    for l in range(batch.num_lines):
+        a, b = fast.line(l), slow.line(l)
+        assert np.abs(a - b).max() <= 1e-11 * np.abs(b).max()
+
+
+def test_edge_inputs(ctx, oracle):
+    from proton_b200.api import LineBatch
+    rng = np.random.default_rng(3)
+    # unsorted triplets with duplicates; zero currents; saturating and tiny a*t
+    li = synth_line(rng, 50, 3)
+    li.rows = np.concatenate([li.rows[::-1], li.rows[:2]]).astype(np.int32)
+    li.cols = np.concatenate([li.cols[::-1], li.cols[:2]]).astype(np.int32)
+    li.vals = np.concatenate([li.vals[::-1], li.vals[:2] * 0.25])
+    z = synth_line(rng, 40, 2)
+    z.curden = np.zeros_like(z.curden)
+    sat = synth_line(rng, 300, 4, a=3.3586e-21 / (0.05e-6) ** 2)
+    tiny = synth_line(rng, 300, 4, a=3.3586e-21 / (40e-6) ** 2)
+    batch = LineBatch.from_lines([li, z, sat, tiny])
+    ts = np.array([1e3, 1e6, 6.38e8])
+    got = ctx.analyze_host(batch, ts, critical=0.0)
+    ws, wm, wa = oracle_batch(oracle, batch, ts)
+    off = batch.node_off
+    T = len(ts)
+    for l in (0, 2, 3):
+        g = got.line(l)
+        w = ws[off[l] * T:off[l + 1] * T].reshape(T, -1)
+        for j in range(T):
+            tol = 1e-9 if not (l == 3 and ts[j] < 1e6) else 1e-6     # F10: cancellation regime is looser
+            assert np.abs(g[j] - w[j]).max() <= tol * np.abs(w[j]).max(), (l, j)
+    assert np.all(got.line(1) == 0.0)
+    # empty batch and T = 0 are no-ops
+    empty = LineBatch(np.zeros(0, np.int32), np.zeros(0), np.zeros(1, np.int64), np.zeros(0, np.int32),
+                      np.zeros(0, np.int32), np.zeros(0), np.zeros(1, np.int64), np.zeros(0))
+    r = ctx.analyze_host(empty, ts)
+    assert r.max_stress.shape == (0, 3)
+
+
+def test_errors_are_reported_not_swallowed(ctx):
+    from proton_b200.api import LineBatch, ProtonEmError
+    rng = np.random.default_rng(5)
+    bad = synth_line(rng, 20, 2)
+    bad.rows[-1] = 20
+    with pytest.raises(ProtonEmError, match="outside"):
+        ctx.pack(LineBatch.from_lines([synth_line(rng, 10, 2), bad]))
+    with pytest.raises(ProtonEmError, match="nodes"):
+        ctx.pack(LineBatch.from_lines([synth_line(rng, 5000, 2)]))
+
+
+def test_device_pointer_api_matches_host_api(ctx):
+    import torch
+    rng = np.random.default_rng(21)
+    batch = synth_batch(rng, [7, 64, 100, 1000, 1024, 33])
+    ts = np.logspace(6, 8, 6)
+    host = ctx.analyze_host(batch, ts, critical=1e7)
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(a).to(dev)
+    plan = ctx.pack_device(tt(batch.num_nodes), tt(batch.a_coeff), tt(batch.trip_off), tt(batch.trip_row),
+                           tt(batch.trip_col), tt(batch.trip_val), tt(batch.u_off), tt(batch.curden))
+    L, T = batch.num_lines, len(ts)
+    stress = torch.empty(batch.total_nodes * T, dtype=torch.float64, device=dev)
+    mx = torch.empty(L * T, dtype=torch.float64, device=dev)
+    amx = torch.empty(L * T, dtype=torch.int32, device=dev)
+    flag = torch.empty(L * T, dtype=torch.uint8, device=dev)
+    plan.eval_device(tt(ts), stress, mx, amx, flag, critical=1e7)
+    ctx.synchronize()
+    assert np.array_equal(stress.cpu().numpy(), host.stress)
+    assert np.array_equal(mx.cpu().numpy().reshape(L, T), host.max_stress)
+    assert np.array_equal(amx.cpu().numpy().reshape(L, T), host.argmax)
+    assert np.array_equal(flag.cpu().numpy().reshape(L, T), host.flag)
+    assert plan.scratch_bytes > 0
+    plan.close()
+
+
+def test_size_independent_properties_large_batch(ctx):
+    """Properties that need no oracle (used at sizes the oracle would take minutes for)."""
+    from proton_b200.api import LineBatch
+    rng = np.random.default_rng(2026)
+    sizes = np.exp(rng.uniform(np.log(16), np.log(4096), 4000)).astype(int)
+    lines = [synth_line(rng, int(n)) for n in sizes]
+    batch = LineBatch.from_lines(lines)
+    ts = np.logspace(6, np.log10(6.38e8), 32)
+    got = ctx.analyze_host(batch, ts, critical=40e6)
+    self_consistent(batch, ts, got, 40e6)
+    T = len(ts)
+    off = batch.node_off
+    # mass conservation: sum(B u) = 0 for these lines  =>  mean stress ~ 0 at every t
+    for l in range(0, batch.num_lines, 37):
+        s = got.line(l)
+        assert np.all(np.abs(s.mean(axis=1)) <= 1e-9 * np.abs(s).max(axis=1) + 1e-300)
+    # linearity in the current densities
+    for li in lines:
+        li.curden = li.curden * 2.0
+    got2 = ctx.analyze_host(LineBatch.from_lines(lines), ts, critical=40e6)
+    assert np.allclose(got2.stress, 2.0 * got.stress, rtol=1e-12, atol=0)
+    # monotone approach to steady state: max stress never decreases in t for constant currents
+    assert np.all(np.diff(got.max_stress, axis=1) >= -1e-9 * np.abs(got.max_stress[:, 1:]))
