@@ -1,0 +1,371 @@
+// em_long.cuh — long lines: transforms that do not fit one CTA's shared memory (P = P1 * 4096 complex
+// points, P1 in {4, 8, 16, 32}; Bluestein lines with 4096 < N <= 65536, power-of-two lines up to 131072).
+//
+// Same mathematics as em_fft.cuh (two timestamps per complex transform, Makhoul permutation, Bluestein
+// with a DIF forward / DIT inverse pair so no reordering pass exists), factored as P = P1 x P2 with
+// P2 = 4096:  element index i = j + q*P2  (column j, row q).
+//   forward  : column pass  y_r[j] = (sum_q x[j + q P2] w_P1^{-qr}) w_P^{-jr}      -> X[r*P2 + j]
+//              row pass     P2-point DIF on every row, product with H, P2-point DIT   (one CTA per row,
+//                           the in-CTA stages of em_fft.cuh)
+//   inverse  : column pass  u[j + q P2] = sum_r (X[r*P2 + j] w_P^{+jr}) w_P1^{+qr}
+// The passes exchange data through a scratch buffer in global memory that is sized to stay resident in
+// the 126 MB L2 (a wave of transforms at a time).  Kernels:
+//   em_long_modal_kernel      Yhat_k(t1), Yhat_k(t2) for every mode of every transform of the wave
+//   em_long_colfwd_kernel     pre-chirp + forward column pass (Bluestein) / chirp input (table build)
+//   em_long_scatter_kernel    power-of-two lines: U_k written where the row DIT expects it
+//   em_long_row_kernel        row pass (forward * H * inverse, forward only, or inverse only)
+//   em_long_colinv_kernel     inverse column pass + post-chirp + de-interleave + stress store + partial max
+//   em_long_reduce_kernel     per-(line, timestamp) max / argmax / flag from the partials
+#pragma once
+#include "em_fft.cuh"
+
+namespace em {
+
+constexpr int kLongLog2P2 = 12;
+constexpr int kLongP2 = 1 << kLongLog2P2;
+constexpr int kLongColsPerCta = 128;
+
+// cos(2 pi m / 32), m in [0, 32)
+__host__ __device__ constexpr double cos32(int m) {
+  m &= 31;
+  if (m > 16) m = 32 - m;            // cos is even around 16
+  const bool neg = m > 8;
+  if (neg) m = 16 - m;
+  const double c = m == 0 ? 1.0 : m == 1 ? 0.98078528040323044913 : m == 2 ? 0.92387953251128675613
+                   : m == 3 ? 0.83146961230254523708 : m == 4 ? 0.70710678118654752440
+                   : m == 5 ? 0.55557023301960222474 : m == 6 ? 0.38268343236508977173
+                   : m == 7 ? 0.19509032201612826785 : 0.0;
+  return neg ? -c : c;
+}
+__host__ __device__ constexpr double sin32(int m) { return cos32(m - 8); }
+
+// Radix-2 recursion on top of Dft<8>: natural order in and out.
+template <int R, int SIGN> struct DftBig {
+  static __device__ __forceinline__ void run(cplx (&v)[R]) {
+    if constexpr (R <= 8) {
+      Dft<R, SIGN>::run(v);
+    } else {
+      cplx e[R / 2], o[R / 2];
+#pragma unroll
+      for (int i = 0; i < R / 2; ++i) { e[i] = v[2 * i]; o[i] = v[2 * i + 1]; }
+      DftBig<R / 2, SIGN>::run(e);
+      DftBig<R / 2, SIGN>::run(o);
+#pragma unroll
+      for (int r = 0; r < R / 2; ++r) {
+        cplx t;
+        if (r == 0) t = o[r];
+        else if (4 * r == R) t = mul_i<SIGN>(o[r]);
+        else {
+          const double c = cos32(r * (32 / R)), s = (double)SIGN * sin32(r * (32 / R));
+          t = cplx{o[r].x * c - o[r].y * s, o[r].x * s + o[r].y * c};
+        }
+        v[r] = cadd(e[r], t);
+        v[r + R / 2] = csub(e[r], t);
+      }
+    }
+  }
+};
+
+struct LongWave {
+  // transforms of this wave: slot s -> (line, timestamp pair)
+  const int* tr_line;
+  const int* tr_pair;
+  int n_tr;
+  int T;
+  const int* num_nodes;
+  const double* a_coeff;
+  const long long* node_off;
+  const int* line_tab;
+  const NTab* tabs;
+  const double* W;
+  const double* ts;
+  const ulonglong2* exp_tab;
+  cplx* ybuf;            // [n_tr][ystride]
+  long long ystride;
+  cplx* x;               // [n_tr][P]
+  double* stress;
+  double* part_v;        // [n_tr][2][colblocks]
+  int* part_i;
+  double* mx; int* amx; unsigned char* flag;
+  double critical;
+};
+
+// ---- modal values for a wave ------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) em_long_modal_kernel(const LongWave w) {
+  __shared__ ulonglong2 exp_tab[kExpTableEntries];
+  for (int i = threadIdx.x; i < kExpTableEntries; i += blockDim.x) exp_tab[i] = w.exp_tab[i];
+  __syncthreads();
+  const int s = blockIdx.y;
+  const int line = w.tr_line[s], pr = w.tr_pair[s];
+  const int N = w.num_nodes[line];
+  const double a = w.a_coeff[line];
+  const double* lam = w.tabs[w.line_tab[line]].lam;
+  const double* W = w.W + w.node_off[line];
+  const double t1 = w.ts[2 * pr];
+  const double t2 = (2 * pr + 1 < w.T) ? w.ts[2 * pr + 1] : t1;
+  const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
+  cplx* y = w.ybuf + (long long)s * w.ystride;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < N; k += gridDim.x * blockDim.x) {
+    const double l = lam[k], wk = W[k];
+    y[k] = cplx{em_modal(l, wk, w1, t1, exp_tab), em_modal(l, wk, w2, t2, exp_tab)};
+  }
+}
+
+// Packed spectrum entry U_k (before the pre-twiddle) from the modal values.
+__device__ __forceinline__ cplx long_zk(const cplx* __restrict__ y, int k, int N) {
+  const cplx yk = y[k];
+  if (k == 0) return yk;
+  const cplx ym = y[N - k];
+  return cplx{yk.x + ym.y, yk.y - ym.x};
+}
+
+// ---- forward column pass (Bluestein) ----------------------------------------------------------------
+// mode 0: x = pre-chirped spectrum of the wave's transforms;  mode 1: x = conj chirp / P (table build,
+// one "transform" per entry of `tabs_build`).
+struct ColParams {
+  LongWave w;
+  int mode;
+  const NTab* tabs_build;
+  int tr_per_cta;
+  const cplx* twl;       // [P1][P2]  w_P^{+j r}  (em_long_twiddle_kernel)
+};
+
+template <int LOG2P1>
+__global__ void __launch_bounds__(256) em_long_twiddle_kernel(cplx* twl) {
+  constexpr int P1 = 1 << LOG2P1;
+  constexpr long long P = (long long)1 << (LOG2P1 + kLongLog2P2);
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P1 * kLongP2) return;
+  const int r = idx / kLongP2, j = idx - r * kLongP2;
+  twl[idx] = em_cis_frac((unsigned long long)j * r * 2ULL, (unsigned long long)P);
+}
+
+// pre / post chirps of a long Bluestein line (the in-CTA classes get theirs from em_tables_kernel).
+__global__ void __launch_bounds__(256) em_long_prepost_kernel(const NTab* tabs_build, int bluestein) {
+  const NTab tab = tabs_build[blockIdx.y];
+  const unsigned long long N = (unsigned long long)tab.n;
+  cplx* pre = const_cast<cplx*>(tab.pre);
+  cplx* post = const_cast<cplx*>(tab.post);
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < (int)N; k += gridDim.x * blockDim.x) {
+    const unsigned long long kk = (unsigned long long)k;
+    if (bluestein) {
+      pre[k] = em_cis_frac((kk + 2ULL * kk * kk) % (4ULL * N), 2ULL * N);
+      post[k] = em_cis_frac((kk * kk) % (2ULL * N), N);
+    } else {
+      pre[k] = em_cis_frac(kk, 2ULL * N);
+    }
+  }
+}
+
+template <int LOG2P1>
+__global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const ColParams p) {
+  constexpr int P1 = 1 << LOG2P1, P2 = kLongP2, LOG2P = LOG2P1 + kLongLog2P2;
+  constexpr long long P = (long long)1 << LOG2P;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][cols]  w_P^{-j r}
+  const int j = blockIdx.x * kLongColsPerCta + threadIdx.x;
+  for (int r = 1; r < P1; ++r) {
+    const cplx c = ldg_cplx(p.twl + (long long)r * P2 + j);
+    twt[r * kLongColsPerCta + threadIdx.x] = cplx{c.x, -c.y};
+  }
+  const int s0 = blockIdx.y * p.tr_per_cta;
+  const int s1 = min(p.w.n_tr, s0 + p.tr_per_cta);
+  for (int s = s0; s < s1; ++s) {
+    cplx v[P1];
+    int N;
+    if (p.mode == 0) {
+      const int line = p.w.tr_line[s];
+      N = p.w.num_nodes[line];
+      const NTab tab = p.w.tabs[p.w.line_tab[line]];
+      const cplx* y = p.w.ybuf + (long long)s * p.w.ystride;
+#pragma unroll
+      for (int q = 0; q < P1; ++q) {
+        const int k = j + q * P2;
+        v[q] = cplx{0.0, 0.0};
+        if (k < N) {
+          const cplx z = long_zk(y, k, N);
+          v[q] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
+        }
+      }
+    } else {
+      const NTab tab = p.tabs_build[s];
+      N = tab.n;
+      const double inv_p = 1.0 / (double)P;
+#pragma unroll
+      for (int q = 0; q < P1; ++q) {
+        const long long i = j + (long long)q * P2;
+        long long d = -1;
+        if (i < N) d = i; else if (P - i < N) d = P - i;
+        v[q] = cplx{0.0, 0.0};
+        if (d >= 0) {
+          const unsigned long long dd = (unsigned long long)d;
+          const cplx c = em_cis_frac((dd * dd) % (2ULL * N), (unsigned long long)N);
+          v[q] = cplx{c.x * inv_p, -c.y * inv_p};
+        }
+      }
+    }
+    DftBig<P1, -1>::run(v);
+    cplx* x = p.w.x + (long long)s * P;
+    x[j] = v[0];
+#pragma unroll
+    for (int r = 1; r < P1; ++r) x[(long long)r * P2 + j] = cmul(v[r], twt[r * kLongColsPerCta + threadIdx.x]);
+  }
+}
+
+// Position (inside the P-point buffer) where the row DIT expects spectrum entry k: row k mod P1, digit-
+// reversed place of k / P1 inside the row.
+template <int LOG2P1> __device__ __forceinline__ long long long_pos(int k) {
+  constexpr int P1 = 1 << LOG2P1;
+  return (long long)(k & (P1 - 1)) * kLongP2 + digit_pos<kLongLog2P2>(k >> LOG2P1);
+}
+
+// ---- power-of-two long lines: write U_k where the inverse expects it --------------------------------
+template <int LOG2P1>
+__global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) {
+  constexpr long long P = (long long)1 << (LOG2P1 + kLongLog2P2);
+  const int s = blockIdx.y;
+  const int line = w.tr_line[s];
+  const int N = w.num_nodes[line];
+  const NTab tab = w.tabs[w.line_tab[line]];
+  const cplx* y = w.ybuf + (long long)s * w.ystride;
+  cplx* x = w.x + (long long)s * P;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < N; k += gridDim.x * blockDim.x) {
+    const cplx z = long_zk(y, k, N);
+    x[long_pos<LOG2P1>(k)] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
+  }
+}
+
+// ---- row pass ------------------------------------------------------------------------------------------
+// mode 0: DIF, * H, DIT (Bluestein);  mode 1: DIF only, result written to `hhat_out` (table build);
+// mode 2: DIT only (power-of-two lines).
+struct RowParams {
+  cplx* x;
+  int log2p1;
+  int mode;
+  const int* tr_line;
+  const int* line_tab;
+  const NTab* tabs;
+  const NTab* tabs_build;
+  const cplx* tw;          // 4096-point twiddles
+};
+
+__global__ void __launch_bounds__(256) em_long_row_kernel(const RowParams p) {
+  constexpr int LOG2P = kLongLog2P2, P2 = kLongP2, NT = 256, NST = plan_n(LOG2P);
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* data = reinterpret_cast<cplx*>(smem_raw);
+  const int tid = threadIdx.x;
+  const int r = blockIdx.x, s = blockIdx.y;
+  const long long P = (long long)P2 << p.log2p1;
+  cplx* row = p.x + (long long)s * P + (long long)r * P2;
+  for (int i = tid; i < P2; i += NT) data[pad_idx<LOG2P>(i)] = row[i];
+  __syncthreads();
+  if (p.mode != 2) {
+    DifStages<LOG2P, 0, NST - 1, NT>::run(data, 1, p.tw, tid);
+    if (p.mode == 1) {
+      fft_stage<LOG2P, stage_radix<LOG2P, NST - 1>(), 0, true, -1, NT>(data, 1, p.tw, tid);
+      __syncthreads();
+      cplx* out = const_cast<cplx*>(p.tabs_build[s].hhat) + (long long)r * P2;
+      for (int i = tid; i < P2; i += NT) out[i] = data[pad_idx<LOG2P>(i)];
+      return;
+    }
+    const cplx* hh = p.tabs[p.line_tab[p.tr_line[s]]].hhat + (long long)r * P2;
+    fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, 1, hh, tid);
+    __syncthreads();
+    DitStages<LOG2P, NST - 2, 0, NT>::run(data, 1, p.tw, tid);
+  } else {
+    DitStages<LOG2P, NST - 1, 0, NT>::run(data, 1, p.tw, tid);
+  }
+  for (int i = tid; i < P2; i += NT) row[i] = data[pad_idx<LOG2P>(i)];
+}
+
+// ---- inverse column pass + epilogue -----------------------------------------------------------------------
+template <int LOG2P1, bool BLUE>
+__global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const ColParams p) {
+  constexpr int P1 = 1 << LOG2P1, P2 = kLongP2, LOG2P = LOG2P1 + kLongLog2P2;
+  constexpr long long P = (long long)1 << LOG2P;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][cols]  w_P^{+j r}
+  __shared__ double red_v[2][kLongColsPerCta / 32];
+  __shared__ int red_i[2][kLongColsPerCta / 32];
+  const int j = blockIdx.x * kLongColsPerCta + threadIdx.x;
+  for (int r = 1; r < P1; ++r) twt[r * kLongColsPerCta + threadIdx.x] = ldg_cplx(p.twl + (long long)r * P2 + j);
+  const int s0 = blockIdx.y * p.tr_per_cta;
+  const int s1 = min(p.w.n_tr, s0 + p.tr_per_cta);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+  for (int s = s0; s < s1; ++s) {
+    const int line = p.w.tr_line[s], pr = p.w.tr_pair[s];
+    const int N = p.w.num_nodes[line];
+    const int halfN = (N + 1) >> 1;
+    const NTab tab = p.w.tabs[p.w.line_tab[line]];
+    const cplx* x = p.w.x + (long long)s * P;
+    cplx v[P1];
+    v[0] = x[j];
+#pragma unroll
+    for (int r = 1; r < P1; ++r) v[r] = cmul(x[(long long)r * P2 + j], twt[r * kLongColsPerCta + threadIdx.x]);
+    DftBig<P1, +1>::run(v);
+    const int T = p.w.T;
+    const int tj1 = 2 * pr, tj2 = 2 * pr + 1;
+    double* d1 = p.w.stress ? p.w.stress + p.w.node_off[line] * (long long)T + (long long)tj1 * N : nullptr;
+    double* d2 = (p.w.stress && tj2 < T) ? d1 + N : nullptr;
+    double b1 = ninf, b2 = ninf;
+    int i1 = 0x7fffffff, i2 = 0x7fffffff;
+#pragma unroll
+    for (int q = 0; q < (BLUE ? P1 / 2 : P1); ++q) {
+      const int m = j + q * P2;
+      if (m < N) {
+        const cplx u = BLUE ? cmul(v[q], ldg_cplx(tab.post + m)) : v[q];
+        const int idx = (m < halfN) ? 2 * m : 2 * (N - 1 - m) + 1;
+        if (d1) __stcs(d1 + idx, u.x);
+        if (d2) __stcs(d2 + idx, u.y);
+        if (u.x > b1 || (u.x == b1 && idx < i1)) { b1 = u.x; i1 = idx; }
+        if (u.y > b2 || (u.y == b2 && idx < i2)) { b2 = u.y; i2 = idx; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double ob1 = __shfl_xor_sync(0xffffffffu, b1, o); const int oi1 = __shfl_xor_sync(0xffffffffu, i1, o);
+      if (ob1 > b1 || (ob1 == b1 && oi1 < i1)) { b1 = ob1; i1 = oi1; }
+      const double ob2 = __shfl_xor_sync(0xffffffffu, b2, o); const int oi2 = __shfl_xor_sync(0xffffffffu, i2, o);
+      if (ob2 > b2 || (ob2 == b2 && oi2 < i2)) { b2 = ob2; i2 = oi2; }
+    }
+    __syncthreads();
+    if (lane == 0) { red_v[0][warp] = b1; red_i[0][warp] = i1; red_v[1][warp] = b2; red_i[1][warp] = i2; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+      double b = red_v[threadIdx.x][0]; int bi = red_i[threadIdx.x][0];
+      for (int q = 1; q < kLongColsPerCta / 32; ++q) {
+        const double ob = red_v[threadIdx.x][q]; const int oi = red_i[threadIdx.x][q];
+        if (ob > b || (ob == b && oi < bi)) { b = ob; bi = oi; }
+      }
+      const long long o = ((long long)s * 2 + threadIdx.x) * gridDim.x + blockIdx.x;
+      p.w.part_v[o] = b; p.w.part_i[o] = bi;
+    }
+  }
+}
+
+// ---- final reduction of the per-column-block partials -----------------------------------------------------
+__global__ void __launch_bounds__(128) em_long_reduce_kernel(const LongWave w, int colblocks) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= 2 * w.n_tr) return;
+  const int s = e >> 1, which = e & 1;
+  const int line = w.tr_line[s];
+  const int tj = 2 * w.tr_pair[s] + which;
+  if (tj >= w.T) return;
+  double b = -__longlong_as_double(0x7ff0000000000000LL);
+  int bi = 0x7fffffff;
+  for (int c = 0; c < colblocks; ++c) {
+    const double ob = w.part_v[(long long)e * colblocks + c];
+    const int oi = w.part_i[(long long)e * colblocks + c];
+    if (ob > b || (ob == b && oi < bi)) { b = ob; bi = oi; }
+  }
+  if (bi == 0x7fffffff) {
+    bi = 0;
+    b = w.stress ? w.stress[w.node_off[line] * (long long)w.T + (long long)tj * w.num_nodes[line]]
+                 : __longlong_as_double(0x7ff8000000000000LL);
+  }
+  const long long o = (long long)line * w.T + tj;
+  w.mx[o] = b; w.amx[o] = bi; w.flag[o] = (b > w.critical) ? 1 : 0;
+}
+
+}  // namespace em

@@ -18,12 +18,14 @@
 #include <sstream>
 #include <string>
 #include <thread>
+#include <map>
 #include <unordered_map>
 #include <vector>
 #include <sys/stat.h>
 #include <cerrno>
 
 #include "em_kernels.cuh"
+#include "em_long.cuh"
 
 namespace {
 
@@ -55,22 +57,26 @@ constexpr int kMinLog2P = 6, kMaxLog2P = 13;
 constexpr int kMaxPow2N = 1 << kMaxLog2P;          // 8192
 constexpr int kMaxBlueN = (1 << (kMaxLog2P - 1));  // 4096: 2N-1 <= 8192
 
-enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_NONE = 3 };
+constexpr int kLongMinLog2P1 = 2, kLongMaxLog2P1 = 5;                       // P = 4096 * {4, 8, 16, 32}
+constexpr int kMaxLongPow2N = em::kLongP2 << kLongMaxLog2P1;                // 131072
+constexpr int kMaxLongBlueN = (em::kLongP2 << kLongMaxLog2P1) / 2;          // 65536: 2N-1 <= 131072
 
-struct ClassOf { LineClass cls; int log2p; };
+enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_LPOW2 = 3, CLS_LBLUE = 4, CLS_NONE = 5 };
+
+struct ClassOf { LineClass cls; int log2p; };   // log2p = log2 of the FFT length P
 
 ClassOf classify(int N) {
   if (N <= em::kSmallMaxN) return {CLS_SMALL, 0};
   if ((N & (N - 1)) == 0) {
-    if (N > kMaxPow2N) return {CLS_NONE, 0};
+    if (N > kMaxLongPow2N) return {CLS_NONE, 0};
     int p = 0;
     while ((1 << p) < N) ++p;
-    return {CLS_POW2, p};
+    return {N <= kMaxPow2N ? CLS_POW2 : CLS_LPOW2, p};
   }
-  if (N > kMaxBlueN) return {CLS_NONE, 0};
+  if (N > kMaxLongBlueN) return {CLS_NONE, 0};
   int p = 0;
-  while ((1 << p) < 2 * N - 1) ++p;
-  return {CLS_BLUE, p};
+  while ((1LL << p) < 2LL * N - 1) ++p;
+  return {N <= kMaxBlueN ? CLS_BLUE : CLS_LBLUE, p};
 }
 
 // Bump allocator for the per-length tables (lives as long as the context).
@@ -133,6 +139,11 @@ struct proton_em_ctx {
   Arena arena;
   std::unordered_map<int, em::NTab> tabs;   // per distinct N, device pointers into the arena
   int64_t launches = 0;
+  // long-line path: column twiddles per P1 and the wave scratch (grown on demand, reused by every call)
+  em::cplx* d_twl[kLongMaxLog2P1 + 1] = {};
+  DevBuf<em::cplx> long_x, long_y;
+  DevBuf<double> long_part_v;
+  DevBuf<int> long_part_i, long_tr_line, long_tr_pair;
 };
 
 struct proton_em_plan {
@@ -230,6 +241,133 @@ int fft_group(bool blue, int log2p) {
   return 1;
 }
 
+// ===================================== long-line path ==========================================
+#define FOR_EACH_LOG2P1(M) M(2) M(3) M(4) M(5)
+
+constexpr size_t kLongRowSmem = em::padded_len<em::kLongLog2P2>() * sizeof(em::cplx);
+inline size_t long_col_smem(int log2p1) { return ((size_t)1 << log2p1) * em::kLongColsPerCta * sizeof(em::cplx); }
+constexpr int kLongColBlocks = em::kLongP2 / em::kLongColsPerCta;
+
+int init_long_attrs() {
+  CU_TRY(cudaFuncSetAttribute(em::em_long_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLongRowSmem));
+#define M(q)                                                                                                              \
+  CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));        \
+  CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));  \
+  CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));
+  FOR_EACH_LOG2P1(M)
+#undef M
+  return PROTON_EM_OK;
+}
+
+// Transforms per wave: keep the P-point work buffers of a wave around half of the 126 MB L2.
+int long_wave_capacity(int log2p) {
+  const long long bytes = ((long long)1 << log2p) * (long long)sizeof(em::cplx);
+  return (int)std::max<long long>(4, std::min<long long>(1024, ((long long)64 << 20) / bytes));
+}
+
+int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long ystride) {
+  const int lp1 = log2p - em::kLongLog2P2;
+  if (lp1 < kLongMinLog2P1 || lp1 > kLongMaxLog2P1) return fail(PROTON_EM_EINVAL, "bad long log2p %d", log2p);
+  if (!ctx->d_twl[lp1]) {
+    const size_t n = ((size_t)1 << lp1) * em::kLongP2;
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_twl[lp1]), n * sizeof(em::cplx)));
+    const int grid = (int)((n + 255) / 256);
+    switch (lp1) {
+#define M(q) case q: em::em_long_twiddle_kernel<q><<<grid, 256, 0, ctx->stream>>>(ctx->d_twl[lp1]); break;
+      FOR_EACH_LOG2P1(M)
+#undef M
+    }
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
+  }
+  const size_t need_x = (size_t)cap << log2p;
+  const size_t need_y = (size_t)cap * (size_t)ystride;
+  const size_t need_p = (size_t)cap * 2 * kLongColBlocks;
+  if (ctx->long_x.n < need_x || ctx->long_y.n < need_y || ctx->long_part_v.n < need_p) {
+    CU_TRY(cudaStreamSynchronize(ctx->stream));     // earlier waves may still use the old buffers
+    if (ctx->long_x.n < need_x) CU_TRY(ctx->long_x.alloc(need_x));
+    if (ctx->long_y.n < need_y) CU_TRY(ctx->long_y.alloc(need_y));
+    if (ctx->long_part_v.n < need_p) { CU_TRY(ctx->long_part_v.alloc(need_p)); CU_TRY(ctx->long_part_i.alloc(need_p)); }
+  }
+  return PROTON_EM_OK;
+}
+
+int launch_long_colfwd(proton_em_ctx* ctx, int lp1, const em::ColParams& cp, int groups) {
+  const dim3 grid(kLongColBlocks, groups);
+  switch (lp1) {
+#define M(q) case q: em::em_long_colfwd_kernel<q><<<grid, em::kLongColsPerCta, long_col_smem(q), ctx->stream>>>(cp); break;
+    FOR_EACH_LOG2P1(M)
+#undef M
+  }
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int launch_long_colinv(proton_em_ctx* ctx, int lp1, bool blue, const em::ColParams& cp, int groups) {
+  const dim3 grid(kLongColBlocks, groups);
+  switch (lp1) {
+#define M(q)                                                                                                        \
+  case q:                                                                                                           \
+    if (blue) em::em_long_colinv_kernel<q, true><<<grid, em::kLongColsPerCta, long_col_smem(q), ctx->stream>>>(cp);  \
+    else em::em_long_colinv_kernel<q, false><<<grid, em::kLongColsPerCta, long_col_smem(q), ctx->stream>>>(cp);      \
+    break;
+    FOR_EACH_LOG2P1(M)
+#undef M
+  }
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int launch_long_scatter(proton_em_ctx* ctx, int lp1, const em::LongWave& w, int maxN) {
+  const dim3 grid(std::min(256, (maxN + 255) / 256), w.n_tr);
+  switch (lp1) {
+#define M(q) case q: em::em_long_scatter_kernel<q><<<grid, 256, 0, ctx->stream>>>(w); break;
+    FOR_EACH_LOG2P1(M)
+#undef M
+  }
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int launch_long_row(proton_em_ctx* ctx, const em::RowParams& rp, int n_tr) {
+  const dim3 grid(1 << rp.log2p1, n_tr);
+  em::em_long_row_kernel<<<grid, 256, kLongRowSmem, ctx->stream>>>(rp);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+// pre / post chirps and the transformed chirp H of new long lengths (all entries share log2p and kind).
+int long_build_tables(proton_em_ctx* ctx, const std::vector<em::NTab>& entries, int log2p, bool blue) {
+  const int lp1 = log2p - em::kLongLog2P2;
+  const int cap = long_wave_capacity(log2p);
+  { int rc = ensure_long(ctx, log2p, cap, 2); if (rc) return rc; }
+  em::NTab* d_e = nullptr;
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&d_e), entries.size() * sizeof(em::NTab)));
+  struct G { em::NTab* p; ~G() { cudaFree(p); } } g{d_e};
+  CU_TRY(cudaMemcpyAsync(d_e, entries.data(), entries.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, ctx->stream));
+  em::em_long_prepost_kernel<<<dim3(64, (unsigned)entries.size()), 256, 0, ctx->stream>>>(d_e, blue ? 1 : 0);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  if (blue) {
+    for (size_t off = 0; off < entries.size(); off += cap) {
+      const int cnt = (int)std::min<size_t>(cap, entries.size() - off);
+      em::ColParams cp{};
+      cp.w.n_tr = cnt; cp.w.x = ctx->long_x.p;
+      cp.mode = 1; cp.tabs_build = d_e + off; cp.tr_per_cta = 1; cp.twl = ctx->d_twl[lp1];
+      { int rc = launch_long_colfwd(ctx, lp1, cp, cnt); if (rc) return rc; }
+      em::RowParams rp{ctx->long_x.p, lp1, 1, nullptr, nullptr, nullptr, d_e + off, ctx->d_tw[em::kLongLog2P2]};
+      { int rc = launch_long_row(ctx, rp, cnt); if (rc) return rc; }
+    }
+  }
+  CU_TRY(cudaStreamSynchronize(ctx->stream));
+  return PROTON_EM_OK;
+}
+
+
 // lambda_k exactly as the reference computes it (form_analytical_solution, bin/EMtool_analytical@0xc4e8):
 // cos((double)k*pi/(double)N) from the HOST libm — the same libm the reference binary links — doubled,
 // minus 2.0.  A device cos would differ in the last bit often enough to break 1e-9 parity where
@@ -281,12 +419,13 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
     t.n = N;
     t.log2p = (c.cls == CLS_POW2 || c.cls == CLS_BLUE) ? c.log2p : 0;
     t.bluestein = c.cls == CLS_BLUE;
-    if (c.cls == CLS_POW2 || c.cls == CLS_BLUE) {
+    if (c.cls == CLS_LPOW2 || c.cls == CLS_LBLUE) { t.log2p = c.log2p; t.bluestein = c.cls == CLS_LBLUE; }
+    if (c.cls != CLS_SMALL) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
       t.pre = static_cast<const em::cplx*>(p);
     }
-    if (c.cls == CLS_BLUE) {
+    if (c.cls == CLS_BLUE || c.cls == CLS_LBLUE) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
       t.post = static_cast<const em::cplx*>(p);
@@ -314,10 +453,21 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
       CU_TRY(e2);
     }
   }
+  for (int blue = 0; blue < 2; ++blue) {
+    for (int p = em::kLongLog2P2 + kLongMinLog2P1; p <= em::kLongLog2P2 + kLongMaxLog2P1; ++p) {
+      std::vector<em::NTab> grp;
+      for (const em::NTab& t : entries)
+        if (t.log2p == p && t.bluestein == blue) grp.push_back(t);
+      if (grp.empty()) continue;
+      int rc = long_build_tables(ctx, grp, p, blue != 0);
+      if (rc) return rc;
+    }
+  }
   CU_TRY(cudaStreamSynchronize(ctx->stream));   // lam upload must finish before `lam` goes away
   for (const em::NTab& t : entries) ctx->tabs[t.n] = t;
   return PROTON_EM_OK;
 }
+
 
 void destroy_plan(proton_em_plan* p) {
   if (!p) return;
@@ -365,6 +515,7 @@ int proton_em_create(proton_em_ctx** out, int device) {
     CU_TRY(cudaMemcpy(ctx->d_tw[p], tw.data(), P * sizeof(em::cplx), cudaMemcpyHostToDevice));
   }
   int rc = init_kernel_attrs();
+  if (rc == PROTON_EM_OK) rc = init_long_attrs();
   if (rc) { proton_em_destroy(ctx); return rc; }
   *out = ctx;
   return PROTON_EM_OK;
@@ -376,6 +527,9 @@ int proton_em_destroy(proton_em_ctx* ctx) {
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   for (auto* p : ctx->d_tw) if (p) cudaFree(p);
+  for (auto* p : ctx->d_twl) if (p) cudaFree(p);
+  ctx->long_x.free(); ctx->long_y.free(); ctx->long_part_v.free(); ctx->long_part_i.free();
+  ctx->long_tr_line.free(); ctx->long_tr_pair.free();
   ctx->arena.release();
   delete ctx;
   return PROTON_EM_OK;
@@ -455,34 +609,31 @@ int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, p
   for (int N : distinct)
     if (classify(N).cls == CLS_NONE)
       return fail(PROTON_EM_EINVAL, "a line has %d nodes; this build handles N <= %d (any N) and powers of two up to %d",
-                  N, kMaxBlueN, kMaxPow2N);
+                  N, kMaxLongBlueN, kMaxLongPow2N);
   { int rc = ensure_tables(ctx, distinct); if (rc) return rc; }
   std::unordered_map<int, int> tab_index;
   std::vector<em::NTab> tabs(distinct.size());
   for (size_t i = 0; i < distinct.size(); ++i) { tabs[i] = ctx->tabs[distinct[i]]; tab_index[distinct[i]] = (int)i; }
   std::vector<int> line_tab(L);
-  // class lists: small, pow2[p], blue[p]
-  std::vector<std::vector<int>> lists(1 + 2 * (kMaxLog2P + 1));
+  // class lists keyed by (class, log2 P)
+  std::map<int, std::vector<int>> lists;
   for (int64_t i = 0; i < L; ++i) {
     const int N = p->num_nodes[i];
     line_tab[i] = tab_index[N];
     const ClassOf c = classify(N);
-    const int slot = c.cls == CLS_SMALL ? 0 : 1 + (c.cls == CLS_BLUE ? kMaxLog2P + 1 : 0) + c.log2p;
-    lists[slot].push_back((int)i);
+    lists[(int)c.cls * 64 + c.log2p].push_back((int)i);
   }
   std::vector<int> class_lines;
   class_lines.reserve(L);
-  for (size_t s = 0; s < lists.size(); ++s) {
-    if (lists[s].empty()) continue;
+  for (auto& kv : lists) {
     proton_em_plan::ClassList cl;
-    if (s == 0) { cl.cls = CLS_SMALL; cl.log2p = 0; }
-    else if ((int)s <= kMaxLog2P + 1) { cl.cls = CLS_POW2; cl.log2p = (int)s - 1; }
-    else { cl.cls = CLS_BLUE; cl.log2p = (int)s - 1 - (kMaxLog2P + 1); }
+    cl.cls = (LineClass)(kv.first / 64);
+    cl.log2p = kv.first % 64;
     // longest lines first inside a class (they are the most expensive items)
-    std::stable_sort(lists[s].begin(), lists[s].end(), [&](int x, int y) { return p->num_nodes[x] > p->num_nodes[y]; });
+    std::stable_sort(kv.second.begin(), kv.second.end(), [&](int x, int y) { return p->num_nodes[x] > p->num_nodes[y]; });
     cl.offset = (int)class_lines.size();
-    cl.count = (int)lists[s].size();
-    class_lines.insert(class_lines.end(), lists[s].begin(), lists[s].end());
+    cl.count = (int)kv.second.size();
+    class_lines.insert(class_lines.end(), kv.second.begin(), kv.second.end());
     p->classes.push_back(cl);
   }
 
@@ -572,6 +723,64 @@ int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, p
   return PROTON_EM_OK;
 }
 
+static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& cl, const double* d_ts, int T,
+                           double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag, double critical) {
+  proton_em_ctx* ctx = p->ctx;
+  const bool blue = cl.cls == CLS_LBLUE;
+  const int lp1 = cl.log2p - em::kLongLog2P2;
+  const int npairs = (T + 1) / 2;
+  const long long n_tr_total = (long long)cl.count * npairs;
+  if (n_tr_total > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many long transforms");
+  // class lines are sorted longest first
+  std::vector<int> lines(cl.count);
+  CU_TRY(cudaMemcpy(lines.data(), p->d_class_lines.p + cl.offset, cl.count * sizeof(int), cudaMemcpyDeviceToHost));
+  int maxN = 0;
+  for (int l : lines) maxN = std::max(maxN, p->num_nodes[l]);
+  const long long ystride = (maxN + 1) & ~1LL;
+  const int cap = (int)std::min<long long>(long_wave_capacity(cl.log2p), n_tr_total);
+  { int rc = ensure_long(ctx, cl.log2p, cap, ystride); if (rc) return rc; }
+  std::vector<int> tr_line((size_t)n_tr_total), tr_pair((size_t)n_tr_total);
+  for (int i = 0; i < cl.count; ++i)
+    for (int pr = 0; pr < npairs; ++pr) { tr_line[(size_t)i * npairs + pr] = lines[i]; tr_pair[(size_t)i * npairs + pr] = pr; }
+  if (ctx->long_tr_line.n < (size_t)n_tr_total) {
+    CU_TRY(cudaStreamSynchronize(ctx->stream));
+    CU_TRY(ctx->long_tr_line.alloc((size_t)n_tr_total));
+    CU_TRY(ctx->long_tr_pair.alloc((size_t)n_tr_total));
+  }
+  CU_TRY(cudaMemcpyAsync(ctx->long_tr_line.p, tr_line.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  CU_TRY(cudaMemcpyAsync(ctx->long_tr_pair.p, tr_pair.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  for (long long s0 = 0; s0 < n_tr_total; s0 += cap) {
+    const int cnt = (int)std::min<long long>(cap, n_tr_total - s0);
+    em::LongWave w{};
+    w.tr_line = ctx->long_tr_line.p + s0; w.tr_pair = ctx->long_tr_pair.p + s0; w.n_tr = cnt; w.T = T;
+    w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
+    w.tabs = p->d_tabs.p; w.W = p->d_W.p; w.ts = d_ts; w.exp_tab = ctx->d_exp;
+    w.ybuf = ctx->long_y.p; w.ystride = ystride; w.x = ctx->long_x.p; w.stress = d_stress;
+    w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
+    w.critical = critical;
+    em::em_long_modal_kernel<<<dim3(std::min(64, (maxN + 255) / 256), cnt), 256, 0, ctx->stream>>>(w);
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
+    const int tpc = std::max(1, cnt / 24);
+    const int groups = (cnt + tpc - 1) / tpc;
+    em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
+    em::RowParams rp{ctx->long_x.p, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
+                     ctx->d_tw[em::kLongLog2P2]};
+    int rc;
+    if (blue) rc = launch_long_colfwd(ctx, lp1, cp, groups);
+    else rc = launch_long_scatter(ctx, lp1, w, maxN);
+    if (rc) return rc;
+    rc = launch_long_row(ctx, rp, cnt);
+    if (rc) return rc;
+    rc = launch_long_colinv(ctx, lp1, blue, cp, groups);
+    if (rc) return rc;
+    em::em_long_reduce_kernel<<<(2 * cnt + 127) / 128, 128, 0, ctx->stream>>>(w, kLongColBlocks);
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
+  }
+  return PROTON_EM_OK;
+}
+
 static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proton_em_opts* opts,
                        double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag) {
   proton_em_ctx* ctx = p->ctx;
@@ -600,6 +809,11 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
       em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, ctx->stream>>>(sp);
       ctx->launches++;
       CU_TRY(cudaGetLastError());
+      continue;
+    }
+    if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) {
+      int rc = eval_long_class(p, cl, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical);
+      if (rc) return rc;
       continue;
     }
     const bool blue = cl.cls == CLS_BLUE;

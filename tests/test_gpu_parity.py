@@ -97,8 +97,9 @@ def test_random_ragged_batch_against_oracle(ctx, oracle):
     # the plan can be evaluated again at other timestamps (and in reduce-only mode)
     got2 = plan.eval(ts[3:5], critical=1e8, want_stress=False)
     assert got2.stress is None
-    assert np.array_equal(got2.max_stress, got.max_stress[:, 3:5])
-    assert np.array_equal(got2.argmax, got.argmax[:, 3:5])
+    # (two timestamps share one complex transform, so a different pairing moves results by rounding only)
+    assert np.allclose(got2.max_stress, got.max_stress[:, 3:5], rtol=1e-12, atol=0)
+    assert (got2.argmax == got.argmax[:, 3:5]).mean() > 0.99
     plan.close()
 
 
