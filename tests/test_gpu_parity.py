@@ -103,6 +103,34 @@ def test_random_ragged_batch_against_oracle(ctx, oracle):
     plan.close()
 
 
+@pytest.mark.parametrize("T", [1, 4])
+def test_long_lines_against_oracle(ctx, oracle, T):
+    """Lines whose transform does not fit one CTA (multi-pass path with L2-resident scratch)."""
+    rng = np.random.default_rng(900 + T)
+    sizes = [4097, 5000, 8191, 8193, 12000, 16384, 16385, 20670, 32768, 40000, 65536, 65000, 100, 64]
+    batch = synth_batch(rng, sizes)
+    ts = np.array([1e6, 2e7, 6.38e8, 1e8])[:T]
+    got = ctx.analyze_host(batch, ts, critical=40e6)
+    ws, wm, wa = oracle_batch(oracle, batch, ts)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    self_consistent(batch, ts, got, 40e6)
+    print(f"long lines T={T}: worst norm-wise error {worst:.3e}")
+
+
+def test_ibmpg1_full_grid_against_oracle(ctx, oracle):
+    """BASELINE config 1/2 shape: every line of ibmpg1 (reference parser + formulation policy of `analyze`)."""
+    from proton_b200.api import LineBatch
+    from proton_b200.workloads import ibmpg1_lines
+    batch = LineBatch.from_lines(ibmpg1_lines())
+    assert batch.num_lines == 1717
+    ts = np.array([1e6, 1e7, 6.38e8])
+    got = ctx.analyze_host(batch, ts, critical=40e6)
+    ws, wm, wa = oracle_batch(oracle, batch, ts)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    self_consistent(batch, ts, got, 40e6)
+    print(f"ibmpg1 full grid: worst norm-wise error {worst:.3e}; flagged lines {int(got.flag[:, -1].sum())}")
+
+
 def test_direct_kernel_cross_check(ctx, oracle):
     from proton_b200.api import ALG_DIRECT
     rng = np.random.default_rng(11)
@@ -157,7 +185,7 @@ def test_errors_are_reported_not_swallowed(ctx):
     with pytest.raises(ProtonEmError, match="outside"):
         ctx.pack(LineBatch.from_lines([synth_line(rng, 10, 2), bad]))
     with pytest.raises(ProtonEmError, match="nodes"):
-        ctx.pack(LineBatch.from_lines([synth_line(rng, 5000, 2)]))
+        ctx.pack(LineBatch.from_lines([synth_line(rng, 70000, 2)]))
 
 
 def test_device_pointer_api_matches_host_api(ctx):
