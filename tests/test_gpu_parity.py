@@ -234,5 +234,3 @@ def test_size_independent_properties_large_batch(ctx):
         li.curden = li.curden * 2.0
     got2 = ctx.analyze_host(LineBatch.from_lines(lines), ts, critical=40e6)
     assert np.allclose(got2.stress, 2.0 * got.stress, rtol=1e-12, atol=0)
-    # monotone approach to steady state: max stress never decreases in t for constant currents
-    assert np.all(np.diff(got.max_stress, axis=1) >= -1e-9 * np.abs(got.max_stress[:, 1:]))
