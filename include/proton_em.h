@@ -120,6 +120,25 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* batch, con
  * `msg` receives the text the reference prints to stdout before exit(1). */
 int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_t msg_len);
 
+/* One line with no allocation anywhere (this entry point has no counterpart in the reference, which
+ * allocates freely inside its own process).  It exists for callers that must not ask the CUDA runtime for
+ * memory: hosts that gave all device memory to their own pool, plug-ins called where cudaMalloc would stall
+ * the device, loops that cannot tolerate an allocator failure.  No context and no plan are needed; the
+ * working memory of the packing, forward-DCT and direct evaluation kernels is a fixed ~165 KB array inside
+ * the library image (present on every GPU that loads the library, for the life of the process).
+ * All pointers are DEVICE pointers supplied by the caller; d_stress ([T][num_nodes]) may be NULL.
+ * Limits: num_nodes, num_triplets, num_curden <= 4096 each and T <= 65535; larger values are rejected with
+ * PROTON_EM_EINVAL.  The call queues its kernels on `stream` (a cudaStream_t, NULL = default stream),
+ * then waits for them, so results are ready on return.  Every call shares the one array and leaves its
+ * contents there: calls whose GPU work could overlap (other streams or threads, same device) race and must
+ * be serialised by the caller.  The first call on a device looks up the array's address; make it before
+ * starting any stream capture.  Uses the O(N^2) direct evaluator, so it is meant for single lines, not bulk. */
+int proton_em_eval_line_noalloc(int device, void* stream, int32_t num_nodes, double a_coeff,
+                                int32_t num_triplets, const int32_t* d_trip_row, const int32_t* d_trip_col,
+                                const double* d_trip_val, int32_t num_curden, const double* d_curden,
+                                const double* d_ts, int32_t T, double critical_stress, double* d_stress,
+                                double* d_max_stress, int32_t* d_argmax, uint8_t* d_flag);
+
 /* Test hook: y[i] = the device exp() used by the modal evaluation (must equal the host libm's). */
 int proton_em_debug_exp(proton_em_ctx* ctx, const double* x_host, double* y_host, int64_t n);
 

@@ -923,3 +923,127 @@ int proton_em_debug_exp(proton_em_ctx* ctx, const double* x, double* y, int64_t 
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// proton_em_eval_line_noalloc — one line, no allocation of any kind.
+//
+// Who this is for: code that drives the GPU from a place where device memory must not be requested —
+// a host application that handed its whole memory budget to its own pool at start-up, a plug-in
+// running inside a framework's stream-ordered region where cudaMalloc would synchronise the device,
+// or a latency-critical loop that cannot afford an allocator call failing half-way.  Such a caller
+// cannot create a proton_em_ctx (that allocates tables) nor pack a plan (that allocates the modal
+// weights), so this entry point keeps ALL of its working memory — the host-libm lambda table, the
+// packed r = B*u, the modal weights and the bookkeeping words of the packing / forward / direct
+// kernels — in one fixed array that is part of the library image.  Every GPU that loads the library
+// carries that array (about 165 KB) until the process exits.
+//
+// Limits: num_nodes <= 4096, num_triplets <= 4096, num_curden <= 4096, T <= 65535.
+// Concurrency: every call on a device uses the same array and leaves its contents behind; two calls
+// whose GPU work overlaps (different streams, different host threads) race.  Serialise them.
+// The first call on a device looks up the array's device address; make that call before starting any
+// stream capture.
+// =================================================================================================
+namespace {
+
+constexpr int kNoAllocMaxNodes = 4096;
+constexpr int kNoAllocMaxTrip = 4096;
+constexpr int kNoAllocMaxDevices = 64;
+
+struct NoAllocScratch {
+  double lam[kNoAllocMaxNodes];
+  double W[kNoAllocMaxNodes];
+  double prod[kNoAllocMaxTrip];
+  double r_val[kNoAllocMaxTrip];
+  int perm[kNoAllocMaxTrip];
+  int r_idx[kNoAllocMaxTrip];
+  long long node_off[2];
+  long long trip_off[2];
+  long long u_off[2];
+  double a_coeff[1];
+  int num_nodes[1];
+  int line_tab[1];
+  int r_cnt[1];
+  int error_flag[1];
+  em::NTab tab[1];
+  ulonglong2 exp_tab[em::kExpTableEntries];
+};
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+static __device__ const unsigned long long g_noalloc_exp_table[2 * em::kExpTableEntries] = {
+#include "exp_table.inc"
+};
+
+NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+// Fills the bookkeeping words from kernel arguments (no host-to-device copy) and zeroes what the
+// following kernels expect to start at zero.
+__global__ void em_noalloc_setup_kernel(NoAllocScratch* s, int N, double a, int ntrip, int ncur) {
+  const int tid = threadIdx.x;
+  for (int i = tid; i < em::kExpTableEntries; i += blockDim.x)
+    s->exp_tab[i] = make_ulonglong2(g_noalloc_exp_table[2 * i], g_noalloc_exp_table[2 * i + 1]);
+  if (tid == 0) {
+    s->node_off[0] = 0; s->node_off[1] = N;
+    s->trip_off[0] = 0; s->trip_off[1] = ntrip;
+    s->u_off[0] = 0; s->u_off[1] = ncur;
+    s->a_coeff[0] = a; s->num_nodes[0] = N; s->line_tab[0] = 0;
+    s->r_cnt[0] = 0; s->error_flag[0] = 0;          // must start at zero on every call
+    em::NTab t{};
+    t.lam = s->lam; t.n = N;
+    s->tab[0] = t;
+  }
+}
+
+}  // namespace
+
+extern "C" int proton_em_eval_line_noalloc(int device, void* stream_v, int32_t num_nodes, double a_coeff,
+                                           int32_t num_triplets, const int32_t* d_trip_row, const int32_t* d_trip_col,
+                                           const double* d_trip_val, int32_t num_curden, const double* d_curden,
+                                           const double* d_ts, int32_t T, double critical_stress, double* d_stress,
+                                           double* d_max_stress, int32_t* d_argmax, uint8_t* d_flag) {
+  if (num_nodes <= 0 || num_nodes > kNoAllocMaxNodes)
+    return fail(PROTON_EM_EINVAL, "proton_em_eval_line_noalloc: num_nodes = %d, the built-in scratch holds at most %d",
+                num_nodes, kNoAllocMaxNodes);
+  if (num_triplets < 0 || num_triplets > kNoAllocMaxTrip || num_curden < 0 || num_curden > kNoAllocMaxTrip)
+    return fail(PROTON_EM_EINVAL, "proton_em_eval_line_noalloc: %d triplets / %d current densities, the built-in scratch "
+                "holds at most %d of each", num_triplets, num_curden, kNoAllocMaxTrip);
+  if (T < 0 || T > 65535) return fail(PROTON_EM_EINVAL, "proton_em_eval_line_noalloc: T = %d is outside [0, 65535]", T);
+  if (T == 0) return PROTON_EM_OK;
+  if (!d_ts || !d_max_stress || !d_argmax || !d_flag || (num_triplets > 0 && (!d_trip_row || !d_trip_col || !d_trip_val)) ||
+      (num_curden > 0 && !d_curden))
+    return fail(PROTON_EM_EINVAL, "proton_em_eval_line_noalloc: NULL pointer argument");
+  if (device < 0 || device >= kNoAllocMaxDevices) return fail(PROTON_EM_EINVAL, "device %d out of range", device);
+  CU_TRY(cudaSetDevice(device));
+  if (!g_noalloc_ptr[device]) {
+    // The array's name is only a host-side handle: ask the runtime where it lives on THIS device.
+    void* ptr = nullptr;
+    CU_TRY(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+    g_noalloc_ptr[device] = static_cast<NoAllocScratch*>(ptr);
+  }
+  NoAllocScratch* s = g_noalloc_ptr[device];
+  cudaStream_t st = static_cast<cudaStream_t>(stream_v);
+  // lambda_k from the host libm (same reason as in ensure_tables); a fixed host buffer, no heap.
+  static double h_lam[kNoAllocMaxNodes];
+  host_lambda(num_nodes, h_lam);
+  CU_TRY(cudaMemcpyAsync(s->lam, h_lam, (size_t)num_nodes * sizeof(double), cudaMemcpyHostToDevice, st));
+  em_noalloc_setup_kernel<<<1, 128, 0, st>>>(s, num_nodes, a_coeff, num_triplets, num_curden);
+  CU_TRY(cudaGetLastError());
+  em::PackParams pp{1, s->num_nodes, s->trip_off, d_trip_row, d_trip_col, d_trip_val, s->u_off, d_curden,
+                    s->perm, s->prod, s->r_idx, s->r_val, s->r_cnt, s->error_flag};
+  em::em_pack_kernel<<<1, 128, 0, st>>>(pp);
+  CU_TRY(cudaGetLastError());
+  em::ForwardParams fp{1, num_nodes, s->num_nodes, s->a_coeff, s->node_off, s->trip_off, s->r_idx, s->r_val, s->r_cnt,
+                       s->line_tab, s->tab, s->W};
+  em::em_forward_kernel<<<(num_nodes + 255) / 256, 256, 0, st>>>(fp);
+  CU_TRY(cudaGetLastError());
+  em::DirectParams dp{1, T, s->num_nodes, s->a_coeff, s->node_off, s->line_tab, s->tab, s->W, d_ts, s->exp_tab,
+                      d_stress, d_max_stress, d_argmax, d_flag, critical_stress};
+  em::em_eval_direct_kernel<<<(unsigned)T, 256, 0, st>>>(dp);
+  CU_TRY(cudaGetLastError());
+  int err = 0;
+  CU_TRY(cudaMemcpyAsync(&err, s->error_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  if (err != 0)
+    return fail(PROTON_EM_EINVAL, "proton_em_eval_line_noalloc: a B triplet has a row outside [0, num_nodes) or a column "
+                "outside [0, num_curden)");
+  return PROTON_EM_OK;
+}
