@@ -49,7 +49,7 @@ struct EvalParams {
   const NTab* tabs;
   const double* W;             // [sum N] folded modal weights (forward kernel)
   const double* ts;            // [T]
-  const cplx* tw;              // [P] e^{+2 pi i m/P}
+  const cplx* tw;              // base twiddles of this P, per stage (stage_tw_offset)
   const ulonglong2* exp_tab;   // [128]
   double* stress;              // may be null (reduce-only)
   double* mx;                  // [L*T]
@@ -109,6 +109,28 @@ template <int LOG2P, int I> __host__ __device__ constexpr int stage_log2s() {
   return s;
 }
 
+// Twiddles: ONE base value per (stage, j), w1 = e^{+2 pi i j / (R S)}, kept in shared memory; the powers
+// w1^q (q < R) are formed in registers with R-2 complex products (the FP64 pipe has the slack, the L1/shared
+// data pipe does not).  Stages with S == 1 need none.
+__host__ __device__ constexpr int stage_tw_count(int log2p, int i) {
+  int s = log2p;
+  for (int j = 0; j <= i; ++j) s -= lg2(plan_radix(log2p, j));
+  return s == 0 ? 0 : (1 << s);
+}
+__host__ __device__ constexpr int stage_tw_offset(int log2p, int i) {
+  int off = 0;
+  for (int j = 0; j < i; ++j) off += stage_tw_count(log2p, j);
+  return off;
+}
+__host__ __device__ constexpr int stage_tw_total(int log2p) { return stage_tw_offset(log2p, plan_n(log2p)); }
+
+// w[q] = w1^q for q = 1..R-1 (w[0] unused).
+template <int RADIX> __device__ __forceinline__ void tw_powers(cplx w1, cplx (&w)[RADIX]) {
+  w[1] = w1;
+  if constexpr (RADIX >= 4) { w[2] = cmul(w1, w1); w[3] = cmul(w[2], w1); }
+  if constexpr (RADIX >= 8) { w[4] = cmul(w[2], w[2]); w[5] = cmul(w[4], w1); w[6] = cmul(w[4], w[2]); w[7] = cmul(w[4], w[3]); }
+}
+
 // Shared-memory index padding (units of 16-byte complex): one pad slot per 8 elements keeps the
 // stride-R accesses of the s = 1 stages conflict-free, one more per P/8 elements does the same for the
 // digit-reversed scatter of the power-of-two path.
@@ -139,15 +161,16 @@ template <int LOG2P, bool BLUE> struct Cfg {
   static constexpr bool ALIAS_STAGE = LOG2P >= 12;       // staging rows reuse the data buffer
   static constexpr size_t data_bytes = (size_t)G * padded_len<LOG2P>() * sizeof(cplx);
   static constexpr size_t stage_bytes = ALIAS_STAGE ? 0 : (size_t)G * 2 * NSTAGE * sizeof(double);
-  static constexpr size_t smem_bytes = kExpTableEntries * sizeof(ulonglong2) + data_bytes + stage_bytes;
+  static constexpr size_t tw_bytes = (size_t)stage_tw_total(LOG2P) * sizeof(cplx);
+  static constexpr size_t head_bytes = kExpTableEntries * sizeof(ulonglong2) + tw_bytes;
+  static constexpr size_t smem_bytes = head_bytes + data_bytes + stage_bytes;
 };
 
 // One in-place stage over the G transforms in flight.
 //   DIF: y = DFT_R(x) then y_r *= w^(j r);   DIT: x_q *= w^(j q) then DFT_R.   w = e^{SIGN 2 pi i / (R S)}.
-template <int LOG2P, int RADIX, int LOG2S, bool DIF, int SIGN, int NT>
+template <int LOG2P, int RADIX, int LOG2S, bool DIF, int SIGN, int NT, int TWOFF>
 __device__ __forceinline__ void fft_stage(cplx* __restrict__ data, int gcount, const cplx* __restrict__ tw, int tid) {
   constexpr int P = 1 << LOG2P, S = 1 << LOG2S, LOG2R = lg2(RADIX), NB = P / RADIX;
-  constexpr int TWMUL = P / (RADIX * S);
   constexpr int BSTEP = NB < NT ? NB : NT;
   constexpr int GSTEP = NB < NT ? NT / NB : 1;
   constexpr int TSTRIDE = padded_len<LOG2P>();
@@ -157,11 +180,8 @@ __device__ __forceinline__ void fft_stage(cplx* __restrict__ data, int gcount, c
     const int base = ((b >> LOG2S) << (LOG2S + LOG2R)) | j;
     cplx w[RADIX];
     if (S > 1) {
-#pragma unroll
-      for (int q = 1; q < RADIX; ++q) {
-        const cplx tv = ldg_cplx(tw + j * q * TWMUL);
-        w[q] = cplx{tv.x, SIGN > 0 ? tv.y : -tv.y};
-      }
+      const cplx tv = tw[TWOFF + j];
+      tw_powers<RADIX>(cplx{tv.x, SIGN > 0 ? tv.y : -tv.y}, w);
     }
     for (int g = g0; g < gcount; g += GSTEP) {
       cplx* d = data + g * TSTRIDE;
@@ -219,7 +239,7 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
 template <int LOG2P, int I, int IEND, int NT> struct DifStages {   // stages I .. IEND-1, SIGN = -1
   static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
     if constexpr (I < IEND) {
-      fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), true, -1, NT>(data, gcount, tw, tid);
+      fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), true, -1, NT, stage_tw_offset(LOG2P, I)>(data, gcount, tw, tid);
       __syncthreads();
       DifStages<LOG2P, I + 1, IEND, NT>::run(data, gcount, tw, tid);
     }
@@ -228,7 +248,7 @@ template <int LOG2P, int I, int IEND, int NT> struct DifStages {   // stages I .
 template <int LOG2P, int I, int ISTOP, int NT> struct DitStages {   // stages I down to ISTOP, SIGN = +1
   static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
     if constexpr (I >= ISTOP) {
-      fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), false, +1, NT>(data, gcount, tw, tid);
+      fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), false, +1, NT, stage_tw_offset(LOG2P, I)>(data, gcount, tw, tid);
       __syncthreads();
       DitStages<LOG2P, I - 1, ISTOP, NT>::run(data, gcount, tw, tid);
     }
@@ -243,11 +263,13 @@ em_eval_fft_kernel(const EvalParams prm) {
   constexpr int TSTRIDE = padded_len<LOG2P>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   ulonglong2* exp_tab = reinterpret_cast<ulonglong2*>(smem_raw);
-  cplx* data = reinterpret_cast<cplx*>(smem_raw + kExpTableEntries * sizeof(ulonglong2));
+  cplx* twb = reinterpret_cast<cplx*>(smem_raw + kExpTableEntries * sizeof(ulonglong2));
+  cplx* data = reinterpret_cast<cplx*>(smem_raw + C::head_bytes);
   double* stage = C::ALIAS_STAGE ? reinterpret_cast<double*>(data)
-                                 : reinterpret_cast<double*>(smem_raw + kExpTableEntries * sizeof(ulonglong2) + C::data_bytes);
+                                 : reinterpret_cast<double*>(smem_raw + C::head_bytes + C::data_bytes);
   const int tid = threadIdx.x;
   for (int i = tid; i < kExpTableEntries; i += NT) exp_tab[i] = prm.exp_tab[i];
+  for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = prm.tw[i];
 
   const int item = blockIdx.x;
   const int li = item / prm.chunks, chunk = item - li * prm.chunks;
@@ -318,12 +340,12 @@ em_eval_fft_kernel(const EvalParams prm) {
     __syncthreads();
     // ---- phase 2: transforms ------------------------------------------------------------------
     if (BLUE) {
-      DifStages<LOG2P, 0, NST - 1, NT>::run(data, gcount, prm.tw, tid);
+      DifStages<LOG2P, 0, NST - 1, NT>::run(data, gcount, twb, tid);
       fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, gcount, tab.hhat, tid);
       __syncthreads();
-      DitStages<LOG2P, NST - 2, 1, NT>::run(data, gcount, prm.tw, tid);
+      DitStages<LOG2P, NST - 2, 1, NT>::run(data, gcount, twb, tid);
     } else {
-      DitStages<LOG2P, NST - 1, 1, NT>::run(data, gcount, prm.tw, tid);
+      DitStages<LOG2P, NST - 1, 1, NT>::run(data, gcount, twb, tid);
     }
     // ---- last DIT stage (radix 8, stride P/8) fused with chirp post-multiply + de-interleave ---
     {
@@ -336,8 +358,7 @@ em_eval_fft_kernel(const EvalParams prm) {
         for (int b = (NB < NT ? tid % NB : tid); b < NB; b += BSTEP) {
           const int j = b;
           cplx w[8];
-#pragma unroll
-          for (int q = 1; q < 8; ++q) w[q] = ldg_cplx(prm.tw + j * q);
+          tw_powers<8>(twb[j], w);
           cplx post[QN];
           if (BLUE) {
 #pragma unroll
@@ -380,8 +401,10 @@ em_eval_fft_kernel(const EvalParams prm) {
           cplx v[8];
 #pragma unroll
           for (int q = 0; q < 8; ++q) v[q] = data[pad_idx<LOG2P>(j + q * S)];
+          cplx w[8];
+          tw_powers<8>(twb[j], w);
 #pragma unroll
-          for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], ldg_cplx(prm.tw + j * q));
+          for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
           Dft<8, +1>::run(v);
 #pragma unroll
           for (int q = 0; q < QN; ++q) {

@@ -169,7 +169,8 @@ template <int LOG2P, bool BLUE>
 __global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT) em_tables_kernel(const TableParams p) {
   constexpr int P = 1 << LOG2P, NT = Cfg<LOG2P, BLUE>::NT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  cplx* data = reinterpret_cast<cplx*>(smem_raw);
+  cplx* twb = reinterpret_cast<cplx*>(smem_raw);
+  cplx* data = twb + stage_tw_total(LOG2P);
   const NTab tab = p.tabs[blockIdx.x];
   const unsigned long long N = (unsigned long long)tab.n;
   cplx* pre = const_cast<cplx*>(tab.pre);
@@ -180,6 +181,7 @@ __global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT) em_tables_kernel(const T
   }
   cplx* post = const_cast<cplx*>(tab.post);
   cplx* hhat = const_cast<cplx*>(tab.hhat);
+  for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = p.tw[i];
   for (int k = tid; k < (int)N; k += NT) {
     const unsigned long long kk = (unsigned long long)k;
     pre[k] = em_cis_frac((kk + 2ULL * kk * kk) % (4ULL * N), 2ULL * N);
@@ -196,7 +198,7 @@ __global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT) em_tables_kernel(const T
     if (j) data[pad_idx<LOG2P>(P - j)] = h;
   }
   __syncthreads();
-  DifStages<LOG2P, 0, plan_n(LOG2P), NT>::run(data, 1, p.tw, tid);
+  DifStages<LOG2P, 0, plan_n(LOG2P), NT>::run(data, 1, twb, tid);
   for (int i = tid; i < P; i += NT) hhat[i] = data[pad_idx<LOG2P>(i)];
 }
 

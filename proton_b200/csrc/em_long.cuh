@@ -246,23 +246,25 @@ struct RowParams {
   const int* line_tab;
   const NTab* tabs;
   const NTab* tabs_build;
-  const cplx* tw;          // 4096-point twiddles
+  const cplx* tw;          // per-stage twiddle tables of the 4096-point transform
 };
 
 __global__ void __launch_bounds__(256) em_long_row_kernel(const RowParams p) {
   constexpr int LOG2P = kLongLog2P2, P2 = kLongP2, NT = 256, NST = plan_n(LOG2P);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  cplx* data = reinterpret_cast<cplx*>(smem_raw);
+  cplx* twb = reinterpret_cast<cplx*>(smem_raw);
+  cplx* data = twb + stage_tw_total(LOG2P);
   const int tid = threadIdx.x;
   const int r = blockIdx.x, s = blockIdx.y;
+  for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = p.tw[i];
   const long long P = (long long)P2 << p.log2p1;
   cplx* row = p.x + (long long)s * P + (long long)r * P2;
   for (int i = tid; i < P2; i += NT) data[pad_idx<LOG2P>(i)] = row[i];
   __syncthreads();
   if (p.mode != 2) {
-    DifStages<LOG2P, 0, NST - 1, NT>::run(data, 1, p.tw, tid);
+    DifStages<LOG2P, 0, NST - 1, NT>::run(data, 1, twb, tid);
     if (p.mode == 1) {
-      fft_stage<LOG2P, stage_radix<LOG2P, NST - 1>(), 0, true, -1, NT>(data, 1, p.tw, tid);
+      fft_stage<LOG2P, stage_radix<LOG2P, NST - 1>(), 0, true, -1, NT, 0>(data, 1, twb, tid);
       __syncthreads();
       cplx* out = const_cast<cplx*>(p.tabs_build[s].hhat) + (long long)r * P2;
       for (int i = tid; i < P2; i += NT) out[i] = data[pad_idx<LOG2P>(i)];
@@ -271,9 +273,9 @@ __global__ void __launch_bounds__(256) em_long_row_kernel(const RowParams p) {
     const cplx* hh = p.tabs[p.line_tab[p.tr_line[s]]].hhat + (long long)r * P2;
     fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, 1, hh, tid);
     __syncthreads();
-    DitStages<LOG2P, NST - 2, 0, NT>::run(data, 1, p.tw, tid);
+    DitStages<LOG2P, NST - 2, 0, NT>::run(data, 1, twb, tid);
   } else {
-    DitStages<LOG2P, NST - 1, 0, NT>::run(data, 1, p.tw, tid);
+    DitStages<LOG2P, NST - 1, 0, NT>::run(data, 1, twb, tid);
   }
   for (int i = tid; i < P2; i += NT) row[i] = data[pad_idx<LOG2P>(i)];
 }

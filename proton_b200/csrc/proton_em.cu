@@ -183,7 +183,7 @@ int set_smem_attr() {
                               (int)em::Cfg<LOG2P, BLUE>::smem_bytes));
   if (BLUE)
     CU_TRY(cudaFuncSetAttribute(em::em_tables_kernel<LOG2P, BLUE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(em::padded_len<LOG2P>() * sizeof(em::cplx))));
+                                (int)((em::padded_len<LOG2P>() + em::stage_tw_total(LOG2P)) * sizeof(em::cplx))));
   return PROTON_EM_OK;
 }
 
@@ -205,7 +205,7 @@ int launch_tables(proton_em_ctx* ctx, int log2p, const em::NTab* d_entries, int 
 #define M(p)                                                                                              \
   case p:                                                                                                 \
     em::em_tables_kernel<p, BLUE><<<count, em::Cfg<p, BLUE>::NT,                                          \
-                                    BLUE ? em::padded_len<p>() * sizeof(em::cplx) : 0, ctx->stream>>>(tp); \
+                                    BLUE ? (em::padded_len<p>() + em::stage_tw_total(p)) * sizeof(em::cplx) : 0, ctx->stream>>>(tp); \
     break;
     FOR_EACH_LOG2P(M)
 #undef M
@@ -244,7 +244,7 @@ int fft_group(bool blue, int log2p) {
 // ===================================== long-line path ==========================================
 #define FOR_EACH_LOG2P1(M) M(2) M(3) M(4) M(5)
 
-constexpr size_t kLongRowSmem = em::padded_len<em::kLongLog2P2>() * sizeof(em::cplx);
+constexpr size_t kLongRowSmem = (em::padded_len<em::kLongLog2P2>() + em::stage_tw_total(em::kLongLog2P2)) * sizeof(em::cplx);
 inline size_t long_col_smem(int log2p1) { return ((size_t)1 << log2p1) * em::kLongColsPerCta * sizeof(em::cplx); }
 constexpr int kLongColBlocks = em::kLongP2 / em::kLongColsPerCta;
 
@@ -503,16 +503,23 @@ int proton_em_create(proton_em_ctx** out, int device) {
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_exp), sizeof(kExpTable)));
   CU_TRY(cudaMemcpy(ctx->d_exp, kExpTable, sizeof(kExpTable), cudaMemcpyHostToDevice));
   for (int p = kMinLog2P; p <= kMaxLog2P; ++p) {
-    const int P = 1 << p;
-    std::vector<em::cplx> tw(P);
+    // base twiddles per stage (em_fft.cuh: stage_tw_offset): e^{+2 pi i j / (R S)}, j < S
+    std::vector<em::cplx> tw((size_t)em::stage_tw_total(p));
     const long double two_pi = 6.283185307179586476925286766559005768L;
-    for (int m = 0; m < P; ++m) {
-      const long double ang = two_pi * (long double)m / (long double)P;
-      tw[m].x = (double)cosl(ang);
-      tw[m].y = (double)sinl(ang);
+    int log2s = p;
+    for (int i = 0; i < em::plan_n(p); ++i) {
+      const int R = em::plan_radix(p, i);
+      log2s -= em::lg2(R);
+      const int S = 1 << log2s;
+      if (S == 1) continue;
+      const int off = em::stage_tw_offset(p, i);
+      for (int j = 0; j < S; ++j) {
+        const long double ang = two_pi * (long double)j / ((long double)R * (long double)S);
+        tw[(size_t)off + j] = em::cplx{(double)cosl(ang), (double)sinl(ang)};
+      }
     }
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tw[p]), P * sizeof(em::cplx)));
-    CU_TRY(cudaMemcpy(ctx->d_tw[p], tw.data(), P * sizeof(em::cplx), cudaMemcpyHostToDevice));
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tw[p]), tw.size() * sizeof(em::cplx)));
+    CU_TRY(cudaMemcpy(ctx->d_tw[p], tw.data(), tw.size() * sizeof(em::cplx), cudaMemcpyHostToDevice));
   }
   int rc = init_kernel_attrs();
   if (rc == PROTON_EM_OK) rc = init_long_attrs();
