@@ -35,7 +35,8 @@ def build_library(force: bool = False, verbose: bool = False) -> Path:
     deps = sources + list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.inc")) + [PKG.parent / "include" / "proton_em.h"]
     if not force and _newer(LIB, deps):
         return LIB
-    cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-o", str(LIB), *[str(s) for s in sources]]
+    extra = os.environ.get("PROTON_EM_NVCC_EXTRA", "").split()
+    cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-shared", "-o", str(LIB), *[str(s) for s in sources]]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     res = subprocess.run(cmd, capture_output=True, text=True)

@@ -137,6 +137,12 @@ template <int RADIX> __device__ __forceinline__ void tw_powers(cplx w1, cplx (&w
 template <int LOG2P> __host__ __device__ constexpr int pad_idx(int p) { return p + (p >> 3) + (p >> (LOG2P - 3)); }
 template <int LOG2P> __host__ __device__ constexpr int padded_len() { return (1 << LOG2P) + (1 << (LOG2P - 3)) + 8; }
 
+// Padded offset of element q of a butterfly relative to its first element: for every stage of the plans above it
+// does not depend on the butterfly, so shared-memory accesses use immediate offsets.
+template <int LOG2P, int LOG2S> __host__ __device__ constexpr int pad_off(int q) {
+  return pad_idx<LOG2P>(q << LOG2S);
+}
+
 // Position where DIF leaves output k (and where DIT expects input k).
 template <int LOG2P> __device__ __forceinline__ int digit_pos(int k) {
   int p = 0;
@@ -154,10 +160,16 @@ template <int LOG2P> __device__ __forceinline__ int digit_pos(int k) {
 // Class configuration: threads per CTA and transforms in flight.
 template <int LOG2P, bool BLUE> struct Cfg {
   static constexpr int P = 1 << LOG2P;
-  static constexpr int NT = LOG2P >= 13 ? 512 : LOG2P == 12 ? 256 : 128;
+#ifndef EM_NT_MID
+#define EM_NT_MID 256
+#endif
+#ifndef EM_G10
+#define EM_G10 2
+#endif
+  static constexpr int NT = LOG2P >= 13 ? 512 : LOG2P == 12 ? 256 : EM_NT_MID;
   // rows of the staging buffer: N <= P (pow2) or N <= P/2 + 1 (Bluestein)
   static constexpr int NSTAGE = BLUE ? (P / 2 + 8) : P;
-  static constexpr int G = LOG2P <= 6 ? 16 : LOG2P <= 8 ? 8 : LOG2P == 9 ? 4 : LOG2P == 10 ? 2 : 1;
+  static constexpr int G = LOG2P <= 6 ? 32 : LOG2P == 7 ? 16 : LOG2P == 8 ? 8 : LOG2P == 9 ? 4 : LOG2P == 10 ? EM_G10 : 1;
   static constexpr bool ALIAS_STAGE = LOG2P >= 12;       // staging rows reuse the data buffer
   static constexpr size_t data_bytes = (size_t)G * padded_len<LOG2P>() * sizeof(cplx);
   static constexpr size_t stage_bytes = ALIAS_STAGE ? 0 : (size_t)G * 2 * NSTAGE * sizeof(double);
@@ -183,11 +195,12 @@ __device__ __forceinline__ void fft_stage(cplx* __restrict__ data, int gcount, c
       const cplx tv = tw[TWOFF + j];
       tw_powers<RADIX>(cplx{tv.x, SIGN > 0 ? tv.y : -tv.y}, w);
     }
+    const int pbase = pad_idx<LOG2P>(base);
     for (int g = g0; g < gcount; g += GSTEP) {
-      cplx* d = data + g * TSTRIDE;
+      cplx* d = data + g * TSTRIDE + pbase;
       cplx v[RADIX];
 #pragma unroll
-      for (int q = 0; q < RADIX; ++q) v[q] = d[pad_idx<LOG2P>(base + q * S)];
+      for (int q = 0; q < RADIX; ++q) v[q] = d[pad_off<LOG2P, LOG2S>(q)];
       if (DIF) {
         Dft<RADIX, SIGN>::run(v);
         if (S > 1) {
@@ -202,7 +215,7 @@ __device__ __forceinline__ void fft_stage(cplx* __restrict__ data, int gcount, c
         Dft<RADIX, SIGN>::run(v);
       }
 #pragma unroll
-      for (int q = 0; q < RADIX; ++q) d[pad_idx<LOG2P>(base + q * S)] = v[q];
+      for (int q = 0; q < RADIX; ++q) d[pad_off<LOG2P, LOG2S>(q)] = v[q];
     }
   }
 }
@@ -220,17 +233,18 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
     cplx h[RADIX];
 #pragma unroll
     for (int q = 0; q < RADIX; ++q) h[q] = ldg_cplx(hhat + base + q);
+    const int pbase = pad_idx<LOG2P>(base);
     for (int g = g0; g < gcount; g += GSTEP) {
-      cplx* d = data + g * TSTRIDE;
+      cplx* d = data + g * TSTRIDE + pbase;
       cplx v[RADIX];
 #pragma unroll
-      for (int q = 0; q < RADIX; ++q) v[q] = d[pad_idx<LOG2P>(base + q)];
+      for (int q = 0; q < RADIX; ++q) v[q] = d[q];
       Dft<RADIX, -1>::run(v);
 #pragma unroll
       for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], h[q]);
       Dft<RADIX, +1>::run(v);
 #pragma unroll
-      for (int q = 0; q < RADIX; ++q) d[pad_idx<LOG2P>(base + q)] = v[q];
+      for (int q = 0; q < RADIX; ++q) d[q] = v[q];
     }
   }
 }
@@ -284,7 +298,6 @@ em_eval_fft_kernel(const EvalParams prm) {
   const int npairs = (T + 1) >> 1;
   const int pair_begin = chunk * prm.pairs_per_chunk;
   const int pair_end = min(npairs, pair_begin + prm.pairs_per_chunk);
-  const int K2 = (N >> 1) + 1;
   const int halfN = (N + 1) >> 1;
   __syncthreads();
 
@@ -292,23 +305,21 @@ em_eval_fft_kernel(const EvalParams prm) {
     const int gcount = min(G, pair_end - pb);
     // ---- phase 1: modal values -> packed complex spectrum U in shared memory -------------------
     {
+      // mode pairs (k, N-k), k = 1 .. KP; the two unpaired modes (k = 0, and k = N/2 for even N) come after
+      const int KP = (N - 1) >> 1;
       int kp0, kstep, g0, gstep;
-      if (K2 >= NT) { kp0 = tid; kstep = NT; g0 = 0; gstep = 1; }
-      else {
-        const int groups = NT / K2;
-        kp0 = tid % K2; kstep = K2; g0 = tid / K2; gstep = groups;
-        if (g0 >= groups) kp0 = K2;
-      }
-      for (int kp = kp0; kp < K2; kp += kstep) {
+      if (KP >= NT) { kp0 = tid + 1; kstep = NT; g0 = 0; gstep = 1; }
+      else if (KP > 0) {
+        const int groups = NT / KP;
+        kp0 = tid % KP + 1; kstep = KP; g0 = tid / KP; gstep = groups;
+        if (g0 >= groups) kp0 = KP + 1;
+      } else { kp0 = 1; kstep = 1; g0 = 0; gstep = 1; }
+      for (int kp = kp0; kp <= KP; kp += kstep) {
         const int k = kp, kk = N - kp;
-        const bool single = (kp == 0) || (kk == k);
-        const double lamk = lam[k], wk = W[k];
-        double lamkk = 0.0, wkk = 0.0;
-        cplx prek = cplx{1.0, 0.0}, prekk = cplx{1.0, 0.0};
-        if (kp != 0) prek = ldg_cplx(tab.pre + k);
-        if (!single) { lamkk = lam[kk]; wkk = W[kk]; prekk = ldg_cplx(tab.pre + kk); }
+        const double lamk = lam[k], wk = W[k], lamkk = lam[kk], wkk = W[kk];
+        const cplx prek = ldg_cplx(tab.pre + k), prekk = ldg_cplx(tab.pre + kk);
         const int posk = pad_idx<LOG2P>(BLUE ? k : digit_pos<LOG2P>(k));
-        const int poskk = single ? 0 : pad_idx<LOG2P>(BLUE ? kk : digit_pos<LOG2P>(kk));
+        const int poskk = pad_idx<LOG2P>(BLUE ? kk : digit_pos<LOG2P>(kk));
         for (int g = g0; g < gcount; g += gstep) {
           const int j1 = 2 * (pb + g);
           const double t1 = prm.ts[j1];
@@ -317,16 +328,24 @@ em_eval_fft_kernel(const EvalParams prm) {
           cplx* d = data + g * TSTRIDE;
           const double y1k = em_modal(lamk, wk, w1, t1, exp_tab);
           const double y2k = em_modal(lamk, wk, w2, t2, exp_tab);
-          if (kp == 0) {
-            d[posk] = cplx{y1k, y2k};
-          } else if (single) {
-            d[posk] = cmul(prek, cplx{y1k + y2k, y2k - y1k});
-          } else {
-            const double y1kk = em_modal(lamkk, wkk, w1, t1, exp_tab);
-            const double y2kk = em_modal(lamkk, wkk, w2, t2, exp_tab);
-            d[posk] = cmul(prek, cplx{y1k + y2kk, y2k - y1kk});
-            d[poskk] = cmul(prekk, cplx{y1kk + y2k, y2kk - y1k});
-          }
+          const double y1kk = em_modal(lamkk, wkk, w1, t1, exp_tab);
+          const double y2kk = em_modal(lamkk, wkk, w2, t2, exp_tab);
+          d[posk] = cmul(prek, cplx{y1k + y2kk, y2k - y1kk});
+          d[poskk] = cmul(prekk, cplx{y1kk + y2k, y2kk - y1k});
+        }
+      }
+      if (tid < 2 * gcount) {
+        const int g = tid >> 1, which = tid & 1;
+        const int k = which ? (N >> 1) : 0;
+        if (which == 0 || (((N & 1) == 0) && N > 1)) {
+          const int j1 = 2 * (pb + g);
+          const double t1 = prm.ts[j1];
+          const double t2 = (j1 + 1 < T) ? prm.ts[j1 + 1] : t1;
+          const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
+          const double y1 = em_modal(lam[k], W[k], w1, t1, exp_tab);
+          const double y2 = em_modal(lam[k], W[k], w2, t2, exp_tab);
+          const int posk = pad_idx<LOG2P>(BLUE ? k : digit_pos<LOG2P>(k));
+          data[g * TSTRIDE + posk] = which ? cmul(ldg_cplx(tab.pre + k), cplx{y1 + y2, y2 - y1}) : cplx{y1, y2};
         }
       }
       if (BLUE) {
@@ -369,10 +388,10 @@ em_eval_fft_kernel(const EvalParams prm) {
             }
           }
           for (int g = g0; g < gcount; g += GSTEP) {
-            cplx* d = data + g * TSTRIDE;
+            const cplx* d = data + g * TSTRIDE + pad_idx<LOG2P>(j);
             cplx v[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) v[q] = d[pad_idx<LOG2P>(j + q * S)];
+            for (int q = 0; q < 8; ++q) v[q] = d[pad_off<LOG2P, LOG2P - 3>(q)];
 #pragma unroll
             for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
             Dft<8, +1>::run(v);
@@ -400,7 +419,7 @@ em_eval_fft_kernel(const EvalParams prm) {
           const int j = tid + it * NT;
           cplx v[8];
 #pragma unroll
-          for (int q = 0; q < 8; ++q) v[q] = data[pad_idx<LOG2P>(j + q * S)];
+          for (int q = 0; q < 8; ++q) v[q] = data[pad_idx<LOG2P>(j) + pad_off<LOG2P, LOG2P - 3>(q)];
           cplx w[8];
           tw_powers<8>(twb[j], w);
 #pragma unroll

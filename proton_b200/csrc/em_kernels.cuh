@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(256) em_eval_direct_kernel(const DirectParams 
       for (int k = k0 + threadIdx.x; k < min(N, k0 + KC); k += 256) {
         double wk = p.W[noff + k];
         if (k > 0) wk = wk + wk;
-        ych[k - k0] = em_modal(lam[k], wk, w, t, exp_tab);
+        ych[k - k0] = em_modal_exact(lam[k], wk, w, t, exp_tab);
       }
       __syncthreads();
       if (n < N) {

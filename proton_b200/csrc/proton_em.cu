@@ -261,8 +261,13 @@ int init_long_attrs() {
 
 // Transforms per wave: keep the P-point work buffers of a wave around half of the 126 MB L2.
 int long_wave_capacity(int log2p) {
+  static long long budget_mb = [] {
+    const char* e = std::getenv("PROTON_EM_LONG_WAVE_MB");
+    const long long v = e ? std::atoll(e) : 0;
+    return v > 0 ? v : 64LL;
+  }();
   const long long bytes = ((long long)1 << log2p) * (long long)sizeof(em::cplx);
-  return (int)std::max<long long>(4, std::min<long long>(1024, ((long long)64 << 20) / bytes));
+  return (int)std::max<long long>(4, std::min<long long>(1024, (budget_mb << 20) / bytes));
 }
 
 int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long ystride) {
