@@ -166,7 +166,7 @@ template <int LOG2P, bool BLUE> struct Cfg {
 #ifndef EM_G10
 #define EM_G10 2
 #endif
-  static constexpr int NT = LOG2P >= 13 ? 512 : LOG2P == 12 ? 256 : EM_NT_MID;
+  static constexpr int NT = LOG2P >= 13 ? 1024 : LOG2P == 12 ? 512 : EM_NT_MID;
   // rows of the staging buffer: N <= P (pow2) or N <= P/2 + 1 (Bluestein)
   static constexpr int NSTAGE = BLUE ? (P / 2 + 8) : P;
   static constexpr int G = LOG2P <= 6 ? 32 : LOG2P == 7 ? 16 : LOG2P == 8 ? 8 : LOG2P == 9 ? 4 : LOG2P == 10 ? EM_G10 : 1;
@@ -270,7 +270,7 @@ template <int LOG2P, int I, int ISTOP, int NT> struct DitStages {   // stages I 
 };
 
 template <int LOG2P, bool BLUE>
-__global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT)
+__global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT, (LOG2P == 12 ? 2 : 1))
 em_eval_fft_kernel(const EvalParams prm) {
   using C = Cfg<LOG2P, BLUE>;
   constexpr int P = C::P, NT = C::NT, G = C::G, NST = plan_n(LOG2P);

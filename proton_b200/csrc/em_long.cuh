@@ -24,6 +24,10 @@ namespace em {
 constexpr int kLongLog2P2 = 12;
 constexpr int kLongP2 = 1 << kLongLog2P2;
 constexpr int kLongColsPerCta = 128;
+#ifndef EM_ROW_NT
+#define EM_ROW_NT 512
+#endif
+constexpr int kLongRowThreads = EM_ROW_NT;
 
 // cos(2 pi m / 32), m in [0, 32)
 __host__ __device__ constexpr double cos32(int m) {
@@ -249,8 +253,8 @@ struct RowParams {
   const cplx* tw;          // per-stage twiddle tables of the 4096-point transform
 };
 
-__global__ void __launch_bounds__(256) em_long_row_kernel(const RowParams p) {
-  constexpr int LOG2P = kLongLog2P2, P2 = kLongP2, NT = 256, NST = plan_n(LOG2P);
+__global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_long_row_kernel(const RowParams p) {
+  constexpr int LOG2P = kLongLog2P2, P2 = kLongP2, NT = kLongRowThreads, NST = plan_n(LOG2P);
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* twb = reinterpret_cast<cplx*>(smem_raw);
   cplx* data = twb + stage_tw_total(LOG2P);

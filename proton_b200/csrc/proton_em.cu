@@ -141,6 +141,9 @@ struct proton_em_ctx {
   int64_t launches = 0;
   // long-line path: column twiddles per P1 and the wave scratch (grown on demand, reused by every call)
   em::cplx* d_twl[kLongMaxLog2P1 + 1] = {};
+  static constexpr int kLanes = 3;          // waves of long transforms run round-robin on these streams
+  cudaStream_t lane[kLanes] = {};
+  cudaEvent_t ev_fork = nullptr, ev_join[kLanes] = {};
   DevBuf<em::cplx> long_x, long_y;
   DevBuf<double> long_part_v;
   DevBuf<int> long_part_i, long_tr_line, long_tr_pair;
@@ -264,7 +267,7 @@ int long_wave_capacity(int log2p) {
   static long long budget_mb = [] {
     const char* e = std::getenv("PROTON_EM_LONG_WAVE_MB");
     const long long v = e ? std::atoll(e) : 0;
-    return v > 0 ? v : 64LL;
+    return v > 0 ? v : 32LL;
   }();
   const long long bytes = ((long long)1 << log2p) * (long long)sizeof(em::cplx);
   return (int)std::max<long long>(4, std::min<long long>(1024, (budget_mb << 20) / bytes));
@@ -285,11 +288,12 @@ int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long ystride) {
     ctx->launches++;
     CU_TRY(cudaGetLastError());
   }
-  const size_t need_x = (size_t)cap << log2p;
-  const size_t need_y = (size_t)cap * (size_t)ystride;
-  const size_t need_p = (size_t)cap * 2 * kLongColBlocks;
+  const size_t lanes = proton_em_ctx::kLanes;
+  const size_t need_x = lanes * ((size_t)cap << log2p);
+  const size_t need_y = lanes * (size_t)cap * (size_t)ystride;
+  const size_t need_p = lanes * (size_t)cap * 2 * kLongColBlocks;
   if (ctx->long_x.n < need_x || ctx->long_y.n < need_y || ctx->long_part_v.n < need_p) {
-    CU_TRY(cudaStreamSynchronize(ctx->stream));     // earlier waves may still use the old buffers
+    CU_TRY(cudaDeviceSynchronize());                // earlier waves may still use the old buffers
     if (ctx->long_x.n < need_x) CU_TRY(ctx->long_x.alloc(need_x));
     if (ctx->long_y.n < need_y) CU_TRY(ctx->long_y.alloc(need_y));
     if (ctx->long_part_v.n < need_p) { CU_TRY(ctx->long_part_v.alloc(need_p)); CU_TRY(ctx->long_part_i.alloc(need_p)); }
@@ -297,10 +301,10 @@ int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long ystride) {
   return PROTON_EM_OK;
 }
 
-int launch_long_colfwd(proton_em_ctx* ctx, int lp1, const em::ColParams& cp, int groups) {
+int launch_long_colfwd(proton_em_ctx* ctx, cudaStream_t st, int lp1, const em::ColParams& cp, int groups) {
   const dim3 grid(kLongColBlocks, groups);
   switch (lp1) {
-#define M(q) case q: em::em_long_colfwd_kernel<q><<<grid, em::kLongColsPerCta, long_col_smem(q), ctx->stream>>>(cp); break;
+#define M(q) case q: em::em_long_colfwd_kernel<q><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp); break;
     FOR_EACH_LOG2P1(M)
 #undef M
   }
@@ -309,13 +313,13 @@ int launch_long_colfwd(proton_em_ctx* ctx, int lp1, const em::ColParams& cp, int
   return PROTON_EM_OK;
 }
 
-int launch_long_colinv(proton_em_ctx* ctx, int lp1, bool blue, const em::ColParams& cp, int groups) {
+int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int lp1, bool blue, const em::ColParams& cp, int groups) {
   const dim3 grid(kLongColBlocks, groups);
   switch (lp1) {
 #define M(q)                                                                                                        \
   case q:                                                                                                           \
-    if (blue) em::em_long_colinv_kernel<q, true><<<grid, em::kLongColsPerCta, long_col_smem(q), ctx->stream>>>(cp);  \
-    else em::em_long_colinv_kernel<q, false><<<grid, em::kLongColsPerCta, long_col_smem(q), ctx->stream>>>(cp);      \
+    if (blue) em::em_long_colinv_kernel<q, true><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp);  \
+    else em::em_long_colinv_kernel<q, false><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp);      \
     break;
     FOR_EACH_LOG2P1(M)
 #undef M
@@ -325,10 +329,10 @@ int launch_long_colinv(proton_em_ctx* ctx, int lp1, bool blue, const em::ColPara
   return PROTON_EM_OK;
 }
 
-int launch_long_scatter(proton_em_ctx* ctx, int lp1, const em::LongWave& w, int maxN) {
+int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int lp1, const em::LongWave& w, int maxN) {
   const dim3 grid(std::min(256, (maxN + 255) / 256), w.n_tr);
   switch (lp1) {
-#define M(q) case q: em::em_long_scatter_kernel<q><<<grid, 256, 0, ctx->stream>>>(w); break;
+#define M(q) case q: em::em_long_scatter_kernel<q><<<grid, 256, 0, st>>>(w); break;
     FOR_EACH_LOG2P1(M)
 #undef M
   }
@@ -337,9 +341,9 @@ int launch_long_scatter(proton_em_ctx* ctx, int lp1, const em::LongWave& w, int 
   return PROTON_EM_OK;
 }
 
-int launch_long_row(proton_em_ctx* ctx, const em::RowParams& rp, int n_tr) {
+int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp, int n_tr) {
   const dim3 grid(1 << rp.log2p1, n_tr);
-  em::em_long_row_kernel<<<grid, 256, kLongRowSmem, ctx->stream>>>(rp);
+  em::em_long_row_kernel<<<grid, em::kLongRowThreads, kLongRowSmem, st>>>(rp);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   return PROTON_EM_OK;
@@ -363,9 +367,9 @@ int long_build_tables(proton_em_ctx* ctx, const std::vector<em::NTab>& entries, 
       em::ColParams cp{};
       cp.w.n_tr = cnt; cp.w.x = ctx->long_x.p;
       cp.mode = 1; cp.tabs_build = d_e + off; cp.tr_per_cta = 1; cp.twl = ctx->d_twl[lp1];
-      { int rc = launch_long_colfwd(ctx, lp1, cp, cnt); if (rc) return rc; }
+      { int rc = launch_long_colfwd(ctx, ctx->stream, lp1, cp, cnt); if (rc) return rc; }
       em::RowParams rp{ctx->long_x.p, lp1, 1, nullptr, nullptr, nullptr, d_e + off, ctx->d_tw[em::kLongLog2P2]};
-      { int rc = launch_long_row(ctx, rp, cnt); if (rc) return rc; }
+      { int rc = launch_long_row(ctx, ctx->stream, rp, cnt); if (rc) return rc; }
     }
   }
   CU_TRY(cudaStreamSynchronize(ctx->stream));
@@ -505,6 +509,11 @@ int proton_em_create(proton_em_ctx** out, int device) {
   CU_TRY(cudaGetDeviceProperties(&prop, device));
   ctx->sm_count = prop.multiProcessorCount;
   CU_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
+    CU_TRY(cudaStreamCreateWithFlags(&ctx->lane[i], cudaStreamNonBlocking));
+    CU_TRY(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
+  }
+  CU_TRY(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_exp), sizeof(kExpTable)));
   CU_TRY(cudaMemcpy(ctx->d_exp, kExpTable, sizeof(kExpTable), cudaMemcpyHostToDevice));
   for (int p = kMinLog2P; p <= kMaxLog2P; ++p) {
@@ -536,6 +545,12 @@ int proton_em_create(proton_em_ctx** out, int device) {
 int proton_em_destroy(proton_em_ctx* ctx) {
   if (!ctx) return PROTON_EM_OK;
   cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
+    if (ctx->lane[i]) cudaStreamDestroy(ctx->lane[i]);
+    if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
+  }
+  if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   for (auto* p : ctx->d_tw) if (p) cudaFree(p);
@@ -761,34 +776,48 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
   }
   CU_TRY(cudaMemcpyAsync(ctx->long_tr_line.p, tr_line.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
   CU_TRY(cudaMemcpyAsync(ctx->long_tr_pair.p, tr_pair.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-  for (long long s0 = 0; s0 < n_tr_total; s0 += cap) {
+  // fork: the lanes start after everything queued so far on the main stream (uploads above included)
+  CU_TRY(cudaEventRecord(ctx->ev_fork, ctx->stream));
+  for (int i = 0; i < proton_em_ctx::kLanes; ++i) CU_TRY(cudaStreamWaitEvent(ctx->lane[i], ctx->ev_fork, 0));
+  int wave = 0;
+  for (long long s0 = 0; s0 < n_tr_total; s0 += cap, ++wave) {
     const int cnt = (int)std::min<long long>(cap, n_tr_total - s0);
+    const int li = wave % proton_em_ctx::kLanes;
+    cudaStream_t st = ctx->lane[li];
+    em::cplx* xbuf = ctx->long_x.p + (size_t)li * ((size_t)cap << cl.log2p);
     em::LongWave w{};
     w.tr_line = ctx->long_tr_line.p + s0; w.tr_pair = ctx->long_tr_pair.p + s0; w.n_tr = cnt; w.T = T;
     w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
     w.tabs = p->d_tabs.p; w.W = p->d_W.p; w.ts = d_ts; w.exp_tab = ctx->d_exp;
-    w.ybuf = ctx->long_y.p; w.ystride = ystride; w.x = ctx->long_x.p; w.stress = d_stress;
-    w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
+    w.ybuf = ctx->long_y.p + (size_t)li * (size_t)cap * (size_t)ystride; w.ystride = ystride; w.x = xbuf; w.stress = d_stress;
+    w.part_v = ctx->long_part_v.p + (size_t)li * (size_t)cap * 2 * kLongColBlocks;
+    w.part_i = ctx->long_part_i.p + (size_t)li * (size_t)cap * 2 * kLongColBlocks;
+    w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
     w.critical = critical;
-    em::em_long_modal_kernel<<<dim3(std::min(64, (maxN + 255) / 256), cnt), 256, 0, ctx->stream>>>(w);
+    em::em_long_modal_kernel<<<dim3(std::min(64, (maxN + 255) / 256), cnt), 256, 0, st>>>(w);
     ctx->launches++;
     CU_TRY(cudaGetLastError());
     const int tpc = std::max(1, cnt / 24);
     const int groups = (cnt + tpc - 1) / tpc;
     em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
-    em::RowParams rp{ctx->long_x.p, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
+    em::RowParams rp{xbuf, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
                      ctx->d_tw[em::kLongLog2P2]};
     int rc;
-    if (blue) rc = launch_long_colfwd(ctx, lp1, cp, groups);
-    else rc = launch_long_scatter(ctx, lp1, w, maxN);
+    if (blue) rc = launch_long_colfwd(ctx, st, lp1, cp, groups);
+    else rc = launch_long_scatter(ctx, st, lp1, w, maxN);
     if (rc) return rc;
-    rc = launch_long_row(ctx, rp, cnt);
+    rc = launch_long_row(ctx, st, rp, cnt);
     if (rc) return rc;
-    rc = launch_long_colinv(ctx, lp1, blue, cp, groups);
+    rc = launch_long_colinv(ctx, st, lp1, blue, cp, groups);
     if (rc) return rc;
-    em::em_long_reduce_kernel<<<(2 * cnt + 127) / 128, 128, 0, ctx->stream>>>(w, kLongColBlocks);
+    em::em_long_reduce_kernel<<<(2 * cnt + 127) / 128, 128, 0, st>>>(w, kLongColBlocks);
     ctx->launches++;
     CU_TRY(cudaGetLastError());
+  }
+  // join: later work on the main stream (next class, caller's copies) waits for every lane
+  for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
+    CU_TRY(cudaEventRecord(ctx->ev_join[i], ctx->lane[i]));
+    CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0));
   }
   return PROTON_EM_OK;
 }
