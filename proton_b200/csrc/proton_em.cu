@@ -144,6 +144,12 @@ struct proton_em_ctx {
   static constexpr int kLanes = 3;          // waves of long transforms run round-robin on these streams
   cudaStream_t lane[kLanes] = {};
   cudaEvent_t ev_fork = nullptr, ev_join[kLanes] = {};
+  // host-buffer path (proton_em_analyze_host): cached device staging, a copy stream, per-buffer events
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_done[2] = {}, ev_copied[2] = {};
+  DevBuf<double> io_stress[2], io_mx, io_ts;
+  DevBuf<int> io_amx;
+  DevBuf<unsigned char> io_flag;
   DevBuf<em::cplx> long_x, long_y;
   DevBuf<double> long_part_v;
   DevBuf<int> long_part_i, long_tr_line, long_tr_pair;
@@ -168,7 +174,10 @@ struct proton_em_plan {
   DevBuf<em::NTab> d_tabs;
   DevBuf<int> d_class_lines;     // concatenated per-class line lists
   struct ClassList { LineClass cls; int log2p; int offset; int count; };
-  std::vector<ClassList> classes;
+  // Lines are evaluated in chunks of contiguous lines (one chunk unless the host path asked for more, so
+  // that the device-to-host copy of one chunk overlaps the evaluation of the next).
+  struct Chunk { int64_t l0, l1; std::vector<ClassList> classes; };
+  std::vector<Chunk> chunks;
   std::vector<long long> node_off;   // host copy
   std::vector<int> num_nodes;        // host copy
 };
@@ -478,6 +487,9 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
 }
 
 
+template <typename T>
+cudaError_t grow(DevBuf<T>& buf, size_t n) { return buf.n >= n ? cudaSuccess : buf.alloc(n); }
+
 void destroy_plan(proton_em_plan* p) {
   if (!p) return;
   p->own_num_nodes.free(); p->own_a.free(); p->own_trip_off.free();
@@ -514,6 +526,11 @@ int proton_em_create(proton_em_ctx** out, int device) {
     CU_TRY(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
   }
   CU_TRY(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+  CU_TRY(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 2; ++i) {
+    CU_TRY(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+    CU_TRY(cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming));
+  }
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_exp), sizeof(kExpTable)));
   CU_TRY(cudaMemcpy(ctx->d_exp, kExpTable, sizeof(kExpTable), cudaMemcpyHostToDevice));
   for (int p = kMinLog2P; p <= kMaxLog2P; ++p) {
@@ -551,6 +568,13 @@ int proton_em_destroy(proton_em_ctx* ctx) {
     if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
   }
   if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  for (int i = 0; i < 2; ++i) {
+    if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+    if (ctx->ev_copied[i]) cudaEventDestroy(ctx->ev_copied[i]);
+    ctx->io_stress[i].free();
+  }
+  ctx->io_mx.free(); ctx->io_ts.free(); ctx->io_amx.free(); ctx->io_flag.free();
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   for (auto* p : ctx->d_tw) if (p) cudaFree(p);
@@ -584,7 +608,13 @@ int64_t proton_em_plan_scratch_bytes(const proton_em_plan* p) {
                    p->d_r_val.bytes() + p->d_W.bytes() + p->d_tabs.bytes() + p->d_class_lines.bytes());
 }
 
+static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out);
+
 int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, proton_em_plan** out) {
+  return pack_impl(ctx, b, location, 0, out);
+}
+
+static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out) {
   if (!ctx || !b || !out) return fail(PROTON_EM_EINVAL, "proton_em_pack: NULL argument");
   *out = nullptr;
   if (location != PROTON_EM_HOST && location != PROTON_EM_DEVICE) return fail(PROTON_EM_EINVAL, "bad location %d", location);
@@ -642,26 +672,39 @@ int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, p
   std::vector<em::NTab> tabs(distinct.size());
   for (size_t i = 0; i < distinct.size(); ++i) { tabs[i] = ctx->tabs[distinct[i]]; tab_index[distinct[i]] = (int)i; }
   std::vector<int> line_tab(L);
-  // class lists keyed by (class, log2 P)
-  std::map<int, std::vector<int>> lists;
-  for (int64_t i = 0; i < L; ++i) {
-    const int N = p->num_nodes[i];
-    line_tab[i] = tab_index[N];
-    const ClassOf c = classify(N);
-    lists[(int)c.cls * 64 + c.log2p].push_back((int)i);
+  // chunks of contiguous lines, and per chunk the class lists keyed by (class, log2 P)
+  {
+    int64_t l0 = 0;
+    while (l0 < L) {
+      int64_t l1 = l0, nodes = 0;
+      while (l1 < L && (l1 == l0 || chunk_nodes <= 0 || nodes + p->num_nodes[l1] <= chunk_nodes)) { nodes += p->num_nodes[l1]; ++l1; }
+      proton_em_plan::Chunk ch;
+      ch.l0 = l0; ch.l1 = l1;
+      p->chunks.push_back(ch);
+      l0 = l1;
+    }
   }
   std::vector<int> class_lines;
   class_lines.reserve(L);
-  for (auto& kv : lists) {
-    proton_em_plan::ClassList cl;
-    cl.cls = (LineClass)(kv.first / 64);
-    cl.log2p = kv.first % 64;
-    // longest lines first inside a class (they are the most expensive items)
-    std::stable_sort(kv.second.begin(), kv.second.end(), [&](int x, int y) { return p->num_nodes[x] > p->num_nodes[y]; });
-    cl.offset = (int)class_lines.size();
-    cl.count = (int)kv.second.size();
-    class_lines.insert(class_lines.end(), kv.second.begin(), kv.second.end());
-    p->classes.push_back(cl);
+  for (auto& ch : p->chunks) {
+    std::map<int, std::vector<int>> lists;
+    for (int64_t i = ch.l0; i < ch.l1; ++i) {
+      const int N = p->num_nodes[i];
+      line_tab[i] = tab_index[N];
+      const ClassOf c = classify(N);
+      lists[(int)c.cls * 64 + c.log2p].push_back((int)i);
+    }
+    for (auto& kv : lists) {
+      proton_em_plan::ClassList cl;
+      cl.cls = (LineClass)(kv.first / 64);
+      cl.log2p = kv.first % 64;
+      // longest lines first inside a class (they are the most expensive items)
+      std::stable_sort(kv.second.begin(), kv.second.end(), [&](int x, int y) { return p->num_nodes[x] > p->num_nodes[y]; });
+      cl.offset = (int)class_lines.size();
+      cl.count = (int)kv.second.size();
+      class_lines.insert(class_lines.end(), kv.second.begin(), kv.second.end());
+      ch.classes.push_back(cl);
+    }
   }
 
   // ---- device copies -----------------------------------------------------------------------
@@ -823,7 +866,8 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
 }
 
 static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proton_em_opts* opts,
-                       double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag) {
+                       double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag,
+                       int chunk_begin = 0, int chunk_end = -1) {
   proton_em_ctx* ctx = p->ctx;
   const double critical = opts ? opts->critical_stress : NAN;
   const int alg = opts ? opts->algorithm : PROTON_EM_ALG_AUTO;
@@ -838,7 +882,9 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
   }
   if (alg != PROTON_EM_ALG_AUTO) return fail(PROTON_EM_EINVAL, "unknown algorithm %d", alg);
   const long long target_items = (long long)ctx->sm_count * 12;
-  for (const auto& cl : p->classes) {
+  if (chunk_end < 0) chunk_end = (int)p->chunks.size();
+  for (int ci = chunk_begin; ci < chunk_end; ++ci)
+  for (const auto& cl : p->chunks[ci].classes) {
     if (cl.cls == CLS_SMALL) {
       int chunks = (int)std::min<long long>(T, std::max<long long>(1, target_items * 4 / cl.count));
       int tpc = (T + chunks - 1) / chunks;
@@ -912,38 +958,54 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const d
                            const proton_em_opts* opts, const proton_em_result* res, int64_t max_device_bytes) {
   if (!ctx || !b || !res) return fail(PROTON_EM_EINVAL, "proton_em_analyze_host: NULL argument");
   if (T <= 0 || b->num_lines <= 0) return PROTON_EM_OK;
-  if (max_device_bytes <= 0) max_device_bytes = (int64_t)16 << 30;
-  const int64_t L = b->num_lines;
-  int64_t l0 = 0;
-  int64_t node_base = 0;
-  while (l0 < L) {
-    int64_t l1 = l0, nodes = 0;
-    while (l1 < L) {
-      const int64_t n = b->num_nodes[l1];
-      if (l1 > l0 && res->stress && (nodes + n) * (int64_t)T * 8 > max_device_bytes) break;
-      nodes += n;
-      ++l1;
-    }
-    proton_em_batch sub = *b;
-    sub.num_lines = l1 - l0;
-    sub.num_nodes = b->num_nodes + l0;
-    sub.a_coeff = b->a_coeff + l0;
-    sub.trip_off = b->trip_off + l0;
-    sub.u_off = b->u_off + l0;
-    proton_em_plan* plan = nullptr;
-    int rc = proton_em_pack(ctx, &sub, PROTON_EM_HOST, &plan);
-    if (rc) return rc;
-    proton_em_result r2;
-    r2.stress = res->stress ? res->stress + node_base * T : nullptr;
-    r2.max_stress = res->max_stress + l0 * T;
-    r2.argmax = res->argmax + l0 * T;
-    r2.flag = res->flag + l0 * T;
-    rc = proton_em_eval(plan, ts, T, opts, &r2, PROTON_EM_HOST);
-    destroy_plan(plan);
-    if (rc) return rc;
-    node_base += nodes;
-    l0 = l1;
+  if (!ts || !res->max_stress || !res->argmax || !res->flag)
+    return fail(PROTON_EM_EINVAL, "proton_em_analyze_host: ts, max_stress, argmax and flag are required");
+  { int rc = set_device(ctx); if (rc) return rc; }
+  // Two device staging buffers for the stress field; a chunk is copied back while the next one is computed.
+  static const int64_t chunk_mb = [] { const char* e = std::getenv("PROTON_EM_CHUNK_MB"); const long long v = e ? std::atoll(e) : 0; return (int64_t)(v > 0 ? v : 256); }();
+  int64_t chunk_bytes = chunk_mb << 20;
+  if (max_device_bytes > 0) chunk_bytes = std::min<int64_t>(chunk_bytes, std::max<int64_t>(max_device_bytes / 2, 1 << 20));
+  const int64_t chunk_nodes = res->stress ? std::max<int64_t>(1, chunk_bytes / (8 * (int64_t)T)) : 0;
+  proton_em_plan* plan = nullptr;
+  { int rc = pack_impl(ctx, b, PROTON_EM_HOST, chunk_nodes, &plan); if (rc) return rc; }
+  struct PG { proton_em_plan* p; ~PG() { destroy_plan(p); } } pg{plan};
+  const int64_t L = plan->L;
+  const size_t LT = (size_t)L * T;
+  int64_t max_nodes = 0;
+  for (const auto& ch : plan->chunks) max_nodes = std::max<int64_t>(max_nodes, plan->node_off[ch.l1] - plan->node_off[ch.l0]);
+  if (ctx->io_stress[0].n < (size_t)max_nodes * T || ctx->io_mx.n < LT || ctx->io_ts.n < (size_t)T) {
+    CU_TRY(cudaDeviceSynchronize());
+    CU_TRY(grow(ctx->io_ts, (size_t)T)); CU_TRY(grow(ctx->io_mx, LT)); CU_TRY(grow(ctx->io_amx, LT)); CU_TRY(grow(ctx->io_flag, LT));
+    if (res->stress) { CU_TRY(grow(ctx->io_stress[0], (size_t)max_nodes * T)); CU_TRY(grow(ctx->io_stress[1], (size_t)max_nodes * T)); }
   }
+  cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
+  CU_TRY(cudaMemcpyAsync(ctx->io_ts.p, ts, T * sizeof(double), cudaMemcpyHostToDevice, st));
+  int rc = PROTON_EM_OK;
+  for (int c = 0; c < (int)plan->chunks.size() && rc == PROTON_EM_OK; ++c) {
+    const auto& ch = plan->chunks[c];
+    const int bi = c & 1;
+    const int64_t n0 = plan->node_off[ch.l0], n1 = plan->node_off[ch.l1];
+    double* d_st = nullptr;
+    if (res->stress) {
+      if (c >= 2) CU_TRY(cudaStreamWaitEvent(st, ctx->ev_copied[bi], 0));   // the buffer's previous chunk has left
+      d_st = ctx->io_stress[bi].p - n0 * (int64_t)T;                         // kernels index by global node offset
+    }
+    rc = eval_device(plan, ctx->io_ts.p, T, opts, d_st, ctx->io_mx.p, ctx->io_amx.p, ctx->io_flag.p, c, c + 1);
+    if (rc) break;
+    if (res->stress) {
+      CU_TRY(cudaEventRecord(ctx->ev_done[bi], st));
+      CU_TRY(cudaStreamWaitEvent(cs, ctx->ev_done[bi], 0));
+      CU_TRY(cudaMemcpyAsync(res->stress + n0 * (int64_t)T, ctx->io_stress[bi].p, (size_t)(n1 - n0) * T * sizeof(double),
+                             cudaMemcpyDeviceToHost, cs));
+      CU_TRY(cudaEventRecord(ctx->ev_copied[bi], cs));
+    }
+  }
+  if (rc) { cudaDeviceSynchronize(); return rc; }
+  CU_TRY(cudaMemcpyAsync(res->max_stress, ctx->io_mx.p, LT * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaMemcpyAsync(res->argmax, ctx->io_amx.p, LT * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaMemcpyAsync(res->flag, ctx->io_flag.p, LT * sizeof(unsigned char), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  CU_TRY(cudaStreamSynchronize(cs));
   return PROTON_EM_OK;
 }
 
