@@ -234,3 +234,27 @@ def test_size_independent_properties_large_batch(ctx):
         li.curden = li.curden * 2.0
     got2 = ctx.analyze_host(LineBatch.from_lines(lines), ts, critical=40e6)
     assert np.allclose(got2.stress, 2.0 * got.stress, rtol=1e-12, atol=0)
+
+
+def test_launcher_writes_the_reference_output_file(oracle, tmp_path):
+    """Level-1 drop-in: bin/EMtool_analytical <analytical.cfg> writes stress_<%f>.txt where the reference does, with
+    the same number of lines and values within 1e-9 (norm-wise) of the reference binary's own file."""
+    import subprocess
+    from pathlib import Path
+    from proton_b200 import build
+    exe = build.build_launcher()
+    rng = np.random.default_rng(314)
+    for N, S, t in ((257, 4, 6.38e8), (1, 1, 1e6), (6000, 9, 1e7)):
+        li = synth_line(rng, N, S)
+        d = tmp_path / f"case{N}" / "input" / "M5_n1_1" / "CuDD_378.0_0.1"
+        cfg = oracle.write_line_inputs(d, li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, t)
+        r = subprocess.run([str(exe), str(cfg)], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0 and r.stdout == "", r.stdout + r.stderr
+        out = Path(str(d).replace("input", "output", 1)) / oracle.stress_filename(t)
+        got = np.array([float(x) for x in out.read_text().split()])
+        assert len(got) == N
+        want, _, _ = oracle.line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, [t])
+        assert np.abs(got - want[0]).max() <= 1e-9 * np.abs(want[0]).max()
+        if oracle.ref_binary_available() and N <= 2000:
+            ref = oracle.reference_binary_line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, t)
+            assert np.abs(got - ref).max() <= 1e-9 * np.abs(ref).max()
