@@ -51,6 +51,7 @@ struct EvalParams {
   const double* ts;            // [T]
   const cplx* tw;              // base twiddles of this P, per stage (stage_tw_offset)
   const ulonglong2* exp_tab;   // [128]
+  const int* pos_tab;          // [P] padded shared-memory position of spectrum entry k for the DIT input (pow2 classes)
   double* stress;              // may be null (reduce-only)
   double* mx;                  // [L*T]
   int* amx;                    // [L*T]
@@ -270,7 +271,7 @@ template <int LOG2P, int I, int ISTOP, int NT> struct DitStages {   // stages I 
 };
 
 template <int LOG2P, bool BLUE>
-__global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT, (LOG2P == 12 ? 2 : 1))
+__global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT, (LOG2P <= 11 ? 3 : LOG2P == 12 ? 2 : 1))
 em_eval_fft_kernel(const EvalParams prm) {
   using C = Cfg<LOG2P, BLUE>;
   constexpr int P = C::P, NT = C::NT, G = C::G, NST = plan_n(LOG2P);
@@ -318,8 +319,8 @@ em_eval_fft_kernel(const EvalParams prm) {
         const int k = kp, kk = N - kp;
         const double lamk = lam[k], wk = W[k], lamkk = lam[kk], wkk = W[kk];
         const cplx prek = ldg_cplx(tab.pre + k), prekk = ldg_cplx(tab.pre + kk);
-        const int posk = pad_idx<LOG2P>(BLUE ? k : digit_pos<LOG2P>(k));
-        const int poskk = pad_idx<LOG2P>(BLUE ? kk : digit_pos<LOG2P>(kk));
+        const int posk = BLUE ? pad_idx<LOG2P>(k) : __ldg(prm.pos_tab + k);
+        const int poskk = BLUE ? pad_idx<LOG2P>(kk) : __ldg(prm.pos_tab + kk);
         for (int g = g0; g < gcount; g += gstep) {
           const int j1 = 2 * (pb + g);
           const double t1 = prm.ts[j1];
@@ -449,21 +450,32 @@ em_eval_fft_kernel(const EvalParams prm) {
       }
     }
     __syncthreads();
-    // ---- phase 3: one warp per (transform, timestamp) row: coalesced store + max / argmax -------
+    // ---- phase 3: coalesced store + max / argmax; every row is split over WPR warps so that all warps of the
+    // CTA take part (with one transform in flight there are only two rows) -------------------------------------
     {
-      const int warp = tid >> 5, lane = tid & 31, nwarps = NT >> 5;
-      for (int rr = warp; rr < 2 * gcount; rr += nwarps) {
+      constexpr int NWARPS = NT >> 5;
+      constexpr int WPR = (NWARPS / (2 * G)) > 1 ? (NWARPS / (2 * G)) : 1;     // warps per row
+      constexpr int RSTEP = NWARPS / WPR;                                       // rows handled per sweep
+      __shared__ double red_v[NWARPS];
+      __shared__ int red_i[NWARPS];
+      const int warp = tid >> 5, lane = tid & 31;
+      const int seg = warp % WPR;
+      const int seglen = (((N + WPR - 1) / WPR) + 31) & ~31;
+      const int n_begin = seg * seglen, n_end = min(N, n_begin + seglen);
+      const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+      for (int rr = warp / WPR; rr < 2 * gcount; rr += RSTEP) {
         const int g = rr >> 1, which = rr & 1;
         const int tj = 2 * (pb + g) + which;
-        if (tj >= T) continue;
         const double* src = stage + (size_t)g * 2 * C::NSTAGE + (size_t)which * C::NSTAGE;
-        double* dst = prm.stress ? prm.stress + noff * (long long)T + (long long)tj * N : nullptr;
-        double best = -__longlong_as_double(0x7ff0000000000000LL);
+        double* dst = (prm.stress && tj < T) ? prm.stress + noff * (long long)T + (long long)tj * N : nullptr;
+        double best = ninf;
         int besti = 0x7fffffff;
-        for (int n = lane; n < N; n += 32) {
-          const double v = src[n];
-          if (dst) __stcs(dst + n, v);
-          if (v > best) { best = v; besti = n; }
+        if (tj < T) {
+          for (int n = n_begin + lane; n < n_end; n += 32) {
+            const double v = src[n];
+            if (dst) __stcs(dst + n, v);
+            if (v > best) { best = v; besti = n; }
+          }
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -471,8 +483,31 @@ em_eval_fft_kernel(const EvalParams prm) {
           const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
           if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
         }
-        if (lane == 0) {
-          if (besti == 0x7fffffff) { besti = 0; best = src[0]; }
+        if (WPR == 1) {
+          if (lane == 0 && tj < T) {
+            if (besti == 0x7fffffff) { besti = 0; best = src[0]; }
+            const long long o = (long long)line * T + tj;
+            prm.mx[o] = best; prm.amx[o] = besti;
+            prm.flag[o] = (best > prm.critical) ? 1 : 0;
+          }
+        } else if (lane == 0) {
+          red_v[warp] = best; red_i[warp] = besti;
+        }
+      }
+      if (WPR > 1) {
+        // WPR > 1 means RSTEP >= 2*G: every warp had at most one row; combine its segments through smem
+        __syncthreads();
+        const int rr = warp / WPR;
+        const int g = rr >> 1, which = rr & 1;
+        const int tj = 2 * (pb + g) + which;
+        if (seg == 0 && lane == 0 && rr < 2 * gcount && tj < T) {
+          double best = red_v[warp];
+          int besti = red_i[warp];
+          for (int q = 1; q < WPR; ++q) {
+            const double ob = red_v[warp + q]; const int oi = red_i[warp + q];
+            if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+          }
+          if (besti == 0x7fffffff) { besti = 0; best = stage[(size_t)g * 2 * C::NSTAGE + (size_t)which * C::NSTAGE]; }
           const long long o = (long long)line * T + tj;
           prm.mx[o] = best; prm.amx[o] = besti;
           prm.flag[o] = (best > prm.critical) ? 1 : 0;

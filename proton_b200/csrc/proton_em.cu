@@ -136,6 +136,7 @@ struct proton_em_ctx {
   cudaStream_t stream = nullptr;
   ulonglong2* d_exp = nullptr;
   em::cplx* d_tw[kMaxLog2P + 1] = {};
+  int* d_pos[kMaxLog2P + 1] = {};           // padded DIT input positions per FFT length (em_fft.cuh: pos_tab)
   Arena arena;
   std::unordered_map<int, em::NTab> tabs;   // per distinct N, device pointers into the arena
   int64_t launches = 0;
@@ -549,6 +550,22 @@ int proton_em_create(proton_em_ctx** out, int device) {
         tw[(size_t)off + j] = em::cplx{(double)cosl(ang), (double)sinl(ang)};
       }
     }
+    {
+      const int P = 1 << p;
+      std::vector<int> pos(P);
+      for (int k = 0; k < P; ++k) {
+        int q = 0, sh = p, kk = k;
+        for (int i = 0; i < em::plan_n(p); ++i) {
+          const int lr = em::lg2(em::plan_radix(p, i));
+          sh -= lr;
+          q |= (kk & ((1 << lr) - 1)) << sh;
+          kk >>= lr;
+        }
+        pos[k] = q + (q >> 3) + (q >> (p - 3));
+      }
+      CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_pos[p]), P * sizeof(int)));
+      CU_TRY(cudaMemcpy(ctx->d_pos[p], pos.data(), P * sizeof(int), cudaMemcpyHostToDevice));
+    }
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_tw[p]), tw.size() * sizeof(em::cplx)));
     CU_TRY(cudaMemcpy(ctx->d_tw[p], tw.data(), tw.size() * sizeof(em::cplx), cudaMemcpyHostToDevice));
   }
@@ -578,6 +595,7 @@ int proton_em_destroy(proton_em_ctx* ctx) {
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   for (auto* p : ctx->d_tw) if (p) cudaFree(p);
+  for (auto* p : ctx->d_pos) if (p) cudaFree(p);
   for (auto* p : ctx->d_twl) if (p) cudaFree(p);
   ctx->long_x.free(); ctx->long_y.free(); ctx->long_part_v.free(); ctx->long_part_i.free();
   ctx->long_tr_line.free(); ctx->long_tr_pair.free();
@@ -913,7 +931,7 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
     chunks = (npairs + ppc - 1) / ppc;
     em::EvalParams ep{p->d_class_lines.p + cl.offset, cl.count, chunks, ppc, T, p->d_num_nodes, p->d_a,
                       p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_tw[cl.log2p], ctx->d_exp,
-                      d_stress, d_mx, d_amx, d_flag, critical};
+                      ctx->d_pos[cl.log2p], d_stress, d_mx, d_amx, d_flag, critical};
     const long long grid = (long long)cl.count * chunks;
     if (grid > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many work items");
     int rc = launch_eval_fft(ctx, blue, cl.log2p, ep, (int)grid);
