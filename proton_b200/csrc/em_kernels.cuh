@@ -113,10 +113,11 @@ __global__ void __launch_bounds__(128) em_pack_kernel(const PackParams p) {
 // ---------------------------------------------------------------------------------------------
 struct ForwardParams {
   long long num_lines;
-  long long total_nodes;
+  long long total_blocks;       // sum over lines of ceil(N / kFwdBlock)
   const int* num_nodes;
   const double* a_coeff;
   const long long* node_off;
+  const long long* blk_off;     // [L+1] prefix sum of ceil(N / kFwdBlock)
   const long long* trip_off;
   const int* r_idx;
   const double* r_val;
@@ -125,6 +126,8 @@ struct ForwardParams {
   const NTab* tabs;
   double* W;
 };
+
+constexpr int kFwdBlock = 32;   // consecutive modes per thread
 
 __device__ __forceinline__ long long find_line(const long long* __restrict__ off, long long L, long long g) {
   long long lo = 0, hi = L;           // off[lo] <= g < off[hi]
@@ -135,25 +138,45 @@ __device__ __forceinline__ long long find_line(const long long* __restrict__ off
   return lo;
 }
 
-__global__ void __launch_bounds__(256) em_forward_kernel(const ForwardParams p) {
-  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < p.total_nodes;
+// One thread per (line, block of 32 consecutive modes).  For every non-zero r_v the cosine of mode k0 is taken
+// from an exactly reduced angle and advanced to k0+1, k0+2, ... by the rotation e^{i pi (2v+1)/(2N)} (one complex
+// product per term instead of a 64-bit modulo and a sincospi); 32 steps add < 1e-14 relative error.
+__global__ void __launch_bounds__(128) em_forward_kernel(const ForwardParams p) {
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < p.total_blocks;
        g += (long long)gridDim.x * blockDim.x) {
-    const long long line = find_line(p.node_off, p.num_lines, g);
+    const long long line = find_line(p.blk_off, p.num_lines, g);
     const int N = p.num_nodes[line];
-    const int k = (int)(g - p.node_off[line]);
+    const int k0 = (int)(g - p.blk_off[line]) * kFwdBlock;
+    const int kn = min(kFwdBlock, N - k0);
     const long long t0 = p.trip_off[line];
     const int cnt = p.r_cnt[line];
     const unsigned long long den = 2ULL * (unsigned long long)N;
-    double R = 0.0;
+    double R[kFwdBlock];
+#pragma unroll
+    for (int i = 0; i < kFwdBlock; ++i) R[i] = 0.0;
     for (int i = 0; i < cnt; ++i) {
-      const unsigned long long v = (unsigned long long)p.r_idx[t0 + i];
-      const unsigned long long num = ((2ULL * v + 1ULL) * (unsigned long long)k) % (2ULL * den);
-      R = fma(p.r_val[t0 + i], em_cos_frac(num, den), R);
+      const unsigned long long m = 2ULL * (unsigned long long)p.r_idx[t0 + i] + 1ULL;   // < 2*den
+      const double rv = p.r_val[t0 + i];
+      const cplx w = em_cis_frac(m, den);
+      cplx z = em_cis_frac((m * (unsigned long long)k0) % (2ULL * den), den);
+#pragma unroll
+      for (int q = 0; q < kFwdBlock; ++q) {
+        R[q] = fma(rv, z.x, R[q]);
+        z = cmul(z, w);
+      }
     }
-    const double lam = p.tabs[p.line_tab[line]].lam[k];
-    double w = R / (double)N;
-    if (lam != 0.0) w = w / __dmul_rn(lam, p.a_coeff[line]);
-    p.W[g] = w;
+    const double* lam = p.tabs[p.line_tab[line]].lam + k0;
+    const double a = p.a_coeff[line];
+    double* W = p.W + p.node_off[line] + k0;
+#pragma unroll
+    for (int q = 0; q < kFwdBlock; ++q) {
+      if (q < kn) {
+        const double l = lam[q];
+        double w = R[q] / (double)N;
+        if (l != 0.0) w = w / __dmul_rn(l, a);
+        W[q] = w;
+      }
+    }
   }
 }
 

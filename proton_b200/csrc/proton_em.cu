@@ -169,7 +169,7 @@ struct proton_em_plan {
   DevBuf<double> own_a;
   DevBuf<long long> own_trip_off;
   // derived
-  DevBuf<long long> d_node_off;
+  DevBuf<long long> d_node_off, d_blk_off;
   DevBuf<int> d_r_idx, d_r_cnt, d_line_tab;
   DevBuf<double> d_r_val, d_W;
   DevBuf<em::NTab> d_tabs;
@@ -494,7 +494,7 @@ cudaError_t grow(DevBuf<T>& buf, size_t n) { return buf.n >= n ? cudaSuccess : b
 void destroy_plan(proton_em_plan* p) {
   if (!p) return;
   p->own_num_nodes.free(); p->own_a.free(); p->own_trip_off.free();
-  p->d_node_off.free(); p->d_r_idx.free(); p->d_r_cnt.free(); p->d_line_tab.free();
+  p->d_node_off.free(); p->d_blk_off.free(); p->d_r_idx.free(); p->d_r_cnt.free(); p->d_line_tab.free();
   p->d_r_val.free(); p->d_W.free(); p->d_tabs.free(); p->d_class_lines.free();
   delete p;
 }
@@ -795,10 +795,15 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
   em::em_pack_kernel<<<pack_grid, 128, 0, st>>>(pp);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
-  em::ForwardParams fp{L, p->total_nodes, p->d_num_nodes, p->d_a, p->d_node_off.p, p->d_trip_off,
+  std::vector<long long> blk_off(L + 1);
+  blk_off[0] = 0;
+  for (int64_t i = 0; i < L; ++i) blk_off[i + 1] = blk_off[i] + (p->num_nodes[i] + em::kFwdBlock - 1) / em::kFwdBlock;
+  CU_TRY(p->d_blk_off.alloc(L + 1));
+  CU_TRY(cudaMemcpyAsync(p->d_blk_off.p, blk_off.data(), (L + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+  em::ForwardParams fp{L, blk_off[L], p->d_num_nodes, p->d_a, p->d_node_off.p, p->d_blk_off.p, p->d_trip_off,
                        p->d_r_idx.p, p->d_r_val.p, p->d_r_cnt.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p};
-  const int fwd_grid = (int)std::min<int64_t>((p->total_nodes + 255) / 256, (int64_t)ctx->sm_count * 32);
-  em::em_forward_kernel<<<fwd_grid, 256, 0, st>>>(fp);
+  const int fwd_grid = (int)std::min<int64_t>((blk_off[L] + 127) / 128, (int64_t)ctx->sm_count * 64);
+  em::em_forward_kernel<<<fwd_grid, 128, 0, st>>>(fp);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   int err = 0;
@@ -1078,6 +1083,7 @@ struct NoAllocScratch {
   int perm[kNoAllocMaxTrip];
   int r_idx[kNoAllocMaxTrip];
   long long node_off[2];
+  long long blk_off[2];
   long long trip_off[2];
   long long u_off[2];
   double a_coeff[1];
@@ -1104,6 +1110,7 @@ __global__ void em_noalloc_setup_kernel(NoAllocScratch* s, int N, double a, int 
     s->exp_tab[i] = make_ulonglong2(g_noalloc_exp_table[2 * i], g_noalloc_exp_table[2 * i + 1]);
   if (tid == 0) {
     s->node_off[0] = 0; s->node_off[1] = N;
+    s->blk_off[0] = 0; s->blk_off[1] = (N + em::kFwdBlock - 1) / em::kFwdBlock;
     s->trip_off[0] = 0; s->trip_off[1] = ntrip;
     s->u_off[0] = 0; s->u_off[1] = ncur;
     s->a_coeff[0] = a; s->num_nodes[0] = N; s->line_tab[0] = 0;
@@ -1152,9 +1159,9 @@ extern "C" int proton_em_eval_line_noalloc(int device, void* stream_v, int32_t n
                     s->perm, s->prod, s->r_idx, s->r_val, s->r_cnt, s->error_flag};
   em::em_pack_kernel<<<1, 128, 0, st>>>(pp);
   CU_TRY(cudaGetLastError());
-  em::ForwardParams fp{1, num_nodes, s->num_nodes, s->a_coeff, s->node_off, s->trip_off, s->r_idx, s->r_val, s->r_cnt,
-                       s->line_tab, s->tab, s->W};
-  em::em_forward_kernel<<<(num_nodes + 255) / 256, 256, 0, st>>>(fp);
+  em::ForwardParams fp{1, (num_nodes + em::kFwdBlock - 1) / em::kFwdBlock, s->num_nodes, s->a_coeff, s->node_off, s->blk_off,
+                       s->trip_off, s->r_idx, s->r_val, s->r_cnt, s->line_tab, s->tab, s->W};
+  em::em_forward_kernel<<<(fp.total_blocks + 127) / 128, 128, 0, st>>>(fp);
   CU_TRY(cudaGetLastError());
   em::DirectParams dp{1, T, s->num_nodes, s->a_coeff, s->node_off, s->line_tab, s->tab, s->W, d_ts, s->exp_tab,
                       d_stress, d_max_stress, d_argmax, d_flag, critical_stress};
