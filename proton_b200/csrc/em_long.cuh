@@ -10,9 +10,8 @@
 //   inverse  : column pass  u[j + q P2] = sum_r (X[r*P2 + j] w_P^{+jr}) w_P1^{+qr}
 // The passes exchange data through a scratch buffer in global memory that is sized to stay resident in
 // the 126 MB L2 (a wave of transforms at a time).  Kernels:
-//   em_long_modal_kernel      Yhat_k(t1), Yhat_k(t2) for every mode of every transform of the wave
-//   em_long_colfwd_kernel     pre-chirp + forward column pass (Bluestein) / chirp input (table build)
-//   em_long_scatter_kernel    power-of-two lines: U_k written where the row DIT expects it
+//   em_long_colfwd_kernel     modal factors + pre-chirp + forward column pass (Bluestein) / chirp input (table build)
+//   em_long_scatter_kernel    power-of-two lines: modal factors, U_k written where the row DIT expects it
 //   em_long_row_kernel        row pass (forward * H * inverse, forward only, or inverse only)
 //   em_long_colinv_kernel     inverse column pass + post-chirp + de-interleave + stress store + partial max
 //   em_long_reduce_kernel     per-(line, timestamp) max / argmax / flag from the partials
@@ -75,6 +74,7 @@ struct LongWave {
   const int* tr_line;
   const int* tr_pair;
   int n_tr;
+  int tr_base;           // index of slot 0 among all transforms of the class (partials are per class)
   int T;
   const int* num_nodes;
   const double* a_coeff;
@@ -84,8 +84,6 @@ struct LongWave {
   const double* W;
   const double* ts;
   const ulonglong2* exp_tab;
-  cplx* ybuf;            // [n_tr][ystride]
-  long long ystride;
   cplx* x;               // [n_tr][P]
   double* stress;
   double* part_v;        // [n_tr][2][colblocks]
@@ -94,33 +92,17 @@ struct LongWave {
   double critical;
 };
 
-// ---- modal values for a wave ------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) em_long_modal_kernel(const LongWave w) {
-  __shared__ ulonglong2 exp_tab[kExpTableEntries];
-  for (int i = threadIdx.x; i < kExpTableEntries; i += blockDim.x) exp_tab[i] = w.exp_tab[i];
-  __syncthreads();
-  const int s = blockIdx.y;
-  const int line = w.tr_line[s], pr = w.tr_pair[s];
-  const int N = w.num_nodes[line];
-  const double a = w.a_coeff[line];
-  const double* lam = w.tabs[w.line_tab[line]].lam;
-  const double* W = w.W + w.node_off[line];
-  const double t1 = w.ts[2 * pr];
-  const double t2 = (2 * pr + 1 < w.T) ? w.ts[2 * pr + 1] : t1;
-  const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
-  cplx* y = w.ybuf + (long long)s * w.ystride;
-  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < N; k += gridDim.x * blockDim.x) {
-    const double l = lam[k], wk = W[k];
-    y[k] = cplx{em_modal(l, wk, w1, t1, exp_tab), em_modal(l, wk, w2, t2, exp_tab)};
-  }
-}
-
-// Packed spectrum entry U_k (before the pre-twiddle) from the modal values.
-__device__ __forceinline__ cplx long_zk(const cplx* __restrict__ y, int k, int N) {
-  const cplx yk = y[k];
-  if (k == 0) return yk;
-  const cplx ym = y[N - k];
-  return cplx{yk.x + ym.y, yk.y - ym.x};
+// Packed spectrum entry Z_k (before the pre-twiddle) straight from lambda / W: the thread evaluates the modal factor
+// of mode k and of its mirror N-k for both timestamps (the mirror's owner does the same; the FP64 pipe has the slack,
+// a separate modal pass through global memory does not pay).
+__device__ __forceinline__ cplx long_zk(const double* __restrict__ lam, const double* __restrict__ W, int k, int N,
+                                        double w1, double t1, double w2, double t2) {
+  const double l = lam[k], wk = W[k];
+  const double y1 = em_modal(l, wk, w1, t1, nullptr), y2 = em_modal(l, wk, w2, t2, nullptr);
+  if (k == 0) return cplx{y1, y2};
+  const double lm = lam[N - k], wm = W[N - k];
+  const double m1 = em_modal(lm, wm, w1, t1, nullptr), m2 = em_modal(lm, wm, w2, t2, nullptr);
+  return cplx{y1 + m2, y2 - m1};
 }
 
 // ---- forward column pass (Bluestein) ----------------------------------------------------------------
@@ -178,16 +160,20 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const C
     cplx v[P1];
     int N;
     if (p.mode == 0) {
-      const int line = p.w.tr_line[s];
+      const int line = p.w.tr_line[s], pr = p.w.tr_pair[s];
       N = p.w.num_nodes[line];
       const NTab tab = p.w.tabs[p.w.line_tab[line]];
-      const cplx* y = p.w.ybuf + (long long)s * p.w.ystride;
+      const double* W = p.w.W + p.w.node_off[line];
+      const double a = p.w.a_coeff[line];
+      const double t1 = p.w.ts[2 * pr];
+      const double t2 = (2 * pr + 1 < p.w.T) ? p.w.ts[2 * pr + 1] : t1;
+      const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
 #pragma unroll
       for (int q = 0; q < P1; ++q) {
         const int k = j + q * P2;
         v[q] = cplx{0.0, 0.0};
-        if (k < N) {
-          const cplx z = long_zk(y, k, N);
+        if (q < P1 / 2 + 1 && k < N) {          // Bluestein: N <= P/2, rows above P1/2 are zero
+          const cplx z = long_zk(tab.lam, W, k, N, w1, t1, w2, t2);
           v[q] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
         }
       }
@@ -231,10 +217,15 @@ __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) 
   const int line = w.tr_line[s];
   const int N = w.num_nodes[line];
   const NTab tab = w.tabs[w.line_tab[line]];
-  const cplx* y = w.ybuf + (long long)s * w.ystride;
+  const double* W = w.W + w.node_off[line];
+  const double a = w.a_coeff[line];
+  const int pr = w.tr_pair[s];
+  const double t1 = w.ts[2 * pr];
+  const double t2 = (2 * pr + 1 < w.T) ? w.ts[2 * pr + 1] : t1;
+  const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
   cplx* x = w.x + (long long)s * P;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < N; k += gridDim.x * blockDim.x) {
-    const cplx z = long_zk(y, k, N);
+    const cplx z = long_zk(tab.lam, W, k, N, w1, t1, w2, t2);
     x[long_pos<LOG2P1>(k)] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
   }
 }
@@ -344,7 +335,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
         const double ob = red_v[threadIdx.x][q]; const int oi = red_i[threadIdx.x][q];
         if (ob > b || (ob == b && oi < bi)) { b = ob; bi = oi; }
       }
-      const long long o = ((long long)s * 2 + threadIdx.x) * gridDim.x + blockIdx.x;
+      const long long o = ((long long)(p.w.tr_base + s) * 2 + threadIdx.x) * gridDim.x + blockIdx.x;
       p.w.part_v[o] = b; p.w.part_i[o] = bi;
     }
   }

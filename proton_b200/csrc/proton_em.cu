@@ -283,7 +283,7 @@ int long_wave_capacity(int log2p) {
   return (int)std::max<long long>(4, std::min<long long>(1024, (budget_mb << 20) / bytes));
 }
 
-int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long ystride) {
+int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long n_tr_total) {
   const int lp1 = log2p - em::kLongLog2P2;
   if (lp1 < kLongMinLog2P1 || lp1 > kLongMaxLog2P1) return fail(PROTON_EM_EINVAL, "bad long log2p %d", log2p);
   if (!ctx->d_twl[lp1]) {
@@ -300,12 +300,10 @@ int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long ystride) {
   }
   const size_t lanes = proton_em_ctx::kLanes;
   const size_t need_x = lanes * ((size_t)cap << log2p);
-  const size_t need_y = lanes * (size_t)cap * (size_t)ystride;
-  const size_t need_p = lanes * (size_t)cap * 2 * kLongColBlocks;
-  if (ctx->long_x.n < need_x || ctx->long_y.n < need_y || ctx->long_part_v.n < need_p) {
+  const size_t need_p = (size_t)std::max<long long>(n_tr_total, 1) * 2 * kLongColBlocks;
+  if (ctx->long_x.n < need_x || ctx->long_part_v.n < need_p) {
     CU_TRY(cudaDeviceSynchronize());                // earlier waves may still use the old buffers
     if (ctx->long_x.n < need_x) CU_TRY(ctx->long_x.alloc(need_x));
-    if (ctx->long_y.n < need_y) CU_TRY(ctx->long_y.alloc(need_y));
     if (ctx->long_part_v.n < need_p) { CU_TRY(ctx->long_part_v.alloc(need_p)); CU_TRY(ctx->long_part_i.alloc(need_p)); }
   }
   return PROTON_EM_OK;
@@ -363,7 +361,7 @@ int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp
 int long_build_tables(proton_em_ctx* ctx, const std::vector<em::NTab>& entries, int log2p, bool blue) {
   const int lp1 = log2p - em::kLongLog2P2;
   const int cap = long_wave_capacity(log2p);
-  { int rc = ensure_long(ctx, log2p, cap, 2); if (rc) return rc; }
+  { int rc = ensure_long(ctx, log2p, cap, 1); if (rc) return rc; }
   em::NTab* d_e = nullptr;
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&d_e), entries.size() * sizeof(em::NTab)));
   struct G { em::NTab* p; ~G() { cudaFree(p); } } g{d_e};
@@ -829,9 +827,8 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
   CU_TRY(cudaMemcpy(lines.data(), p->d_class_lines.p + cl.offset, cl.count * sizeof(int), cudaMemcpyDeviceToHost));
   int maxN = 0;
   for (int l : lines) maxN = std::max(maxN, p->num_nodes[l]);
-  const long long ystride = (maxN + 1) & ~1LL;
   const int cap = (int)std::min<long long>(long_wave_capacity(cl.log2p), n_tr_total);
-  { int rc = ensure_long(ctx, cl.log2p, cap, ystride); if (rc) return rc; }
+  { int rc = ensure_long(ctx, cl.log2p, cap, n_tr_total); if (rc) return rc; }
   std::vector<int> tr_line((size_t)n_tr_total), tr_pair((size_t)n_tr_total);
   for (int i = 0; i < cl.count; ++i)
     for (int pr = 0; pr < npairs; ++pr) { tr_line[(size_t)i * npairs + pr] = lines[i]; tr_pair[(size_t)i * npairs + pr] = pr; }
@@ -855,14 +852,10 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
     w.tr_line = ctx->long_tr_line.p + s0; w.tr_pair = ctx->long_tr_pair.p + s0; w.n_tr = cnt; w.T = T;
     w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
     w.tabs = p->d_tabs.p; w.W = p->d_W.p; w.ts = d_ts; w.exp_tab = ctx->d_exp;
-    w.ybuf = ctx->long_y.p + (size_t)li * (size_t)cap * (size_t)ystride; w.ystride = ystride; w.x = xbuf; w.stress = d_stress;
-    w.part_v = ctx->long_part_v.p + (size_t)li * (size_t)cap * 2 * kLongColBlocks;
-    w.part_i = ctx->long_part_i.p + (size_t)li * (size_t)cap * 2 * kLongColBlocks;
+    w.x = xbuf; w.stress = d_stress; w.tr_base = (int)s0;
+    w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p;
     w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
     w.critical = critical;
-    em::em_long_modal_kernel<<<dim3(std::min(64, (maxN + 255) / 256), cnt), 256, 0, st>>>(w);
-    ctx->launches++;
-    CU_TRY(cudaGetLastError());
     const int tpc = std::max(1, cnt / 24);
     const int groups = (cnt + tpc - 1) / tpc;
     em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
@@ -876,14 +869,21 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
     if (rc) return rc;
     rc = launch_long_colinv(ctx, st, lp1, blue, cp, groups);
     if (rc) return rc;
-    em::em_long_reduce_kernel<<<(2 * cnt + 127) / 128, 128, 0, st>>>(w, kLongColBlocks);
-    ctx->launches++;
-    CU_TRY(cudaGetLastError());
   }
   // join: later work on the main stream (next class, caller's copies) waits for every lane
   for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
     CU_TRY(cudaEventRecord(ctx->ev_join[i], ctx->lane[i]));
     CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0));
+  }
+  {   // one reduction of the column-block partials for the whole class
+    em::LongWave w{};
+    w.tr_line = ctx->long_tr_line.p; w.tr_pair = ctx->long_tr_pair.p; w.n_tr = (int)n_tr_total; w.T = T;
+    w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
+    w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
+    w.critical = critical;
+    em::em_long_reduce_kernel<<<(unsigned)((2 * n_tr_total + 127) / 128), 128, 0, ctx->stream>>>(w, kLongColBlocks);
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
   }
   return PROTON_EM_OK;
 }
