@@ -33,7 +33,7 @@ struct NTab {
   int n;
   int log2p;            // FFT length class (0 = not on the in-CTA FFT path)
   int bluestein;
-  int pad_;
+  int p1;               // long classes: rows of 4096 points per transform (0 otherwise)
 };
 
 struct EvalParams {

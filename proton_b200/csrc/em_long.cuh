@@ -69,6 +69,42 @@ template <int R, int SIGN> struct DftBig {
   }
 };
 
+// Twiddles of the small column DFTs whose length is not a power of two: kDftTw[P1][m] = e^{+2 pi i m / P1}
+// (filled by the host at context creation).  Indices are compile-time constants after unrolling, so the values
+// are read as constant-bank operands.
+constexpr int kLongMaxP1 = 32;
+__constant__ cplx kDftTw[kLongMaxP1 + 1][kLongMaxP1];
+
+// Column DFT of any length R <= 32: radix-2 recursion for powers of two, the plain O(R^2) sum otherwise (the column
+// kernels wait on memory, not on the FP64 pipe).
+template <int R, int SIGN> struct DftAny {
+  static __device__ __forceinline__ void run(cplx (&v)[R]) {
+    if constexpr ((R & (R - 1)) == 0) {
+      DftBig<R, SIGN>::run(v);
+    } else {
+      cplx y[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        cplx acc = v[0];
+#pragma unroll
+        for (int q = 1; q < R; ++q) {
+          const int m = (q * r) % R;
+          if (m == 0) acc = cadd(acc, v[q]);
+          else {
+            const cplx w = kDftTw[R][m];
+            const double wy = SIGN > 0 ? w.y : -w.y;
+            acc.x = fma(v[q].x, w.x, fma(-v[q].y, wy, acc.x));
+            acc.y = fma(v[q].x, wy, fma(v[q].y, w.x, acc.y));
+          }
+        }
+        y[r] = acc;
+      }
+#pragma unroll
+      for (int r = 0; r < R; ++r) v[r] = y[r];
+    }
+  }
+};
+
 struct LongWave {
   // transforms of this wave: slot s -> (line, timestamp pair)
   const int* tr_line;
@@ -116,10 +152,8 @@ struct ColParams {
   const cplx* twl;       // [P1][P2]  w_P^{+j r}  (em_long_twiddle_kernel)
 };
 
-template <int LOG2P1>
-__global__ void __launch_bounds__(256) em_long_twiddle_kernel(cplx* twl) {
-  constexpr int P1 = 1 << LOG2P1;
-  constexpr long long P = (long long)1 << (LOG2P1 + kLongLog2P2);
+__global__ void __launch_bounds__(256) em_long_twiddle_kernel(cplx* twl, int P1) {
+  const long long P = (long long)P1 * kLongP2;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P1 * kLongP2) return;
   const int r = idx / kLongP2, j = idx - r * kLongP2;
@@ -143,10 +177,10 @@ __global__ void __launch_bounds__(256) em_long_prepost_kernel(const NTab* tabs_b
   }
 }
 
-template <int LOG2P1>
+template <int P1>
 __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const ColParams p) {
-  constexpr int P1 = 1 << LOG2P1, P2 = kLongP2, LOG2P = LOG2P1 + kLongLog2P2;
-  constexpr long long P = (long long)1 << LOG2P;
+  constexpr int P2 = kLongP2;
+  constexpr long long P = (long long)P1 * P2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][cols]  w_P^{-j r}
   const int j = blockIdx.x * kLongColsPerCta + threadIdx.x;
@@ -172,7 +206,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const C
       for (int q = 0; q < P1; ++q) {
         const int k = j + q * P2;
         v[q] = cplx{0.0, 0.0};
-        if (q < P1 / 2 + 1 && k < N) {          // Bluestein: N <= P/2, rows above P1/2 are zero
+        if (q < (P1 + 1) / 2 + 1 && k < N) {    // Bluestein: 2N-1 <= P, rows above P1/2 are zero
           const cplx z = long_zk(tab.lam, W, k, N, w1, t1, w2, t2);
           v[q] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
         }
@@ -194,7 +228,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const C
         }
       }
     }
-    DftBig<P1, -1>::run(v);
+    DftAny<P1, -1>::run(v);
     cplx* x = p.w.x + (long long)s * P;
     x[j] = v[0];
 #pragma unroll
@@ -235,7 +269,7 @@ __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) 
 // mode 2: DIT only (power-of-two lines).
 struct RowParams {
   cplx* x;
-  int log2p1;
+  int p1;                  // rows per transform
   int mode;
   const int* tr_line;
   const int* line_tab;
@@ -252,7 +286,7 @@ __global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_lo
   const int tid = threadIdx.x;
   const int r = blockIdx.x, s = blockIdx.y;
   for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = p.tw[i];
-  const long long P = (long long)P2 << p.log2p1;
+  const long long P = (long long)P2 * p.p1;
   cplx* row = p.x + (long long)s * P + (long long)r * P2;
   for (int i = tid; i < P2; i += NT) data[pad_idx<LOG2P>(i)] = row[i];
   __syncthreads();
@@ -276,10 +310,10 @@ __global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_lo
 }
 
 // ---- inverse column pass + epilogue -----------------------------------------------------------------------
-template <int LOG2P1, bool BLUE>
+template <int P1, bool BLUE>
 __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const ColParams p) {
-  constexpr int P1 = 1 << LOG2P1, P2 = kLongP2, LOG2P = LOG2P1 + kLongLog2P2;
-  constexpr long long P = (long long)1 << LOG2P;
+  constexpr int P2 = kLongP2;
+  constexpr long long P = (long long)P1 * P2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][cols]  w_P^{+j r}
   __shared__ double red_v[2][kLongColsPerCta / 32];
@@ -300,7 +334,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
     v[0] = x[j];
 #pragma unroll
     for (int r = 1; r < P1; ++r) v[r] = cmul(x[(long long)r * P2 + j], twt[r * kLongColsPerCta + threadIdx.x]);
-    DftBig<P1, +1>::run(v);
+    DftAny<P1, +1>::run(v);
     const int T = p.w.T;
     const int tj1 = 2 * pr, tj2 = 2 * pr + 1;
     double* d1 = p.w.stress ? p.w.stress + p.w.node_off[line] * (long long)T + (long long)tj1 * N : nullptr;
@@ -308,7 +342,8 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
     double b1 = ninf, b2 = ninf;
     int i1 = 0x7fffffff, i2 = 0x7fffffff;
 #pragma unroll
-    for (int q = 0; q < (BLUE ? P1 / 2 : P1); ++q) {
+    for (int q = 0; q < (BLUE ? (P1 + 1) / 2 + 1 : P1); ++q) {
+      if (BLUE && q >= P1) break;
       const int m = j + q * P2;
       if (m < N) {
         const cplx u = BLUE ? cmul(v[q], ldg_cplx(tab.post + m)) : v[q];

@@ -57,26 +57,35 @@ constexpr int kMinLog2P = 6, kMaxLog2P = 13;
 constexpr int kMaxPow2N = 1 << kMaxLog2P;          // 8192
 constexpr int kMaxBlueN = (1 << (kMaxLog2P - 1));  // 4096: 2N-1 <= 8192
 
-constexpr int kLongMinLog2P1 = 2, kLongMaxLog2P1 = 5;                       // P = 4096 * {4, 8, 16, 32}
-constexpr int kMaxLongPow2N = em::kLongP2 << kLongMaxLog2P1;                // 131072
-constexpr int kMaxLongBlueN = (em::kLongP2 << kLongMaxLog2P1) / 2;          // 65536: 2N-1 <= 131072
+// Long lines: P = P1 * 4096 with P1 from this list (any P1 works for Bluestein; powers of two for 2^p lines).
+constexpr int kLongP1List[] = {3, 4, 5, 6, 7, 8, 10, 12, 14, 16, 20, 24, 28, 32};
+constexpr int kMaxLongPow2N = em::kLongP2 * em::kLongMaxP1;                 // 131072
+constexpr int kMaxLongBlueN = (em::kLongP2 * em::kLongMaxP1) / 2;           // 65536: 2N-1 <= 131072
 
 enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_LPOW2 = 3, CLS_LBLUE = 4, CLS_NONE = 5 };
 
-struct ClassOf { LineClass cls; int log2p; };   // log2p = log2 of the FFT length P
+// log2p = log2 of the FFT length for the in-CTA classes; for the long classes it holds P1 (rows of 4096 points).
+struct ClassOf { LineClass cls; int log2p; };
 
 ClassOf classify(int N) {
   if (N <= em::kSmallMaxN) return {CLS_SMALL, 0};
   if ((N & (N - 1)) == 0) {
     if (N > kMaxLongPow2N) return {CLS_NONE, 0};
+    if (N > kMaxPow2N) return {CLS_LPOW2, N / em::kLongP2};
     int p = 0;
     while ((1 << p) < N) ++p;
-    return {N <= kMaxPow2N ? CLS_POW2 : CLS_LPOW2, p};
+    return {CLS_POW2, p};
   }
   if (N > kMaxLongBlueN) return {CLS_NONE, 0};
+  if (N > kMaxBlueN) {
+    const long long need = 2LL * N - 1;
+    for (int p1 : kLongP1List)
+      if ((long long)p1 * em::kLongP2 >= need) return {CLS_LBLUE, p1};
+    return {CLS_NONE, 0};
+  }
   int p = 0;
   while ((1LL << p) < 2LL * N - 1) ++p;
-  return {N <= kMaxBlueN ? CLS_BLUE : CLS_LBLUE, p};
+  return {CLS_BLUE, p};
 }
 
 // Bump allocator for the per-length tables (lives as long as the context).
@@ -141,7 +150,7 @@ struct proton_em_ctx {
   std::unordered_map<int, em::NTab> tabs;   // per distinct N, device pointers into the arena
   int64_t launches = 0;
   // long-line path: column twiddles per P1 and the wave scratch (grown on demand, reused by every call)
-  em::cplx* d_twl[kLongMaxLog2P1 + 1] = {};
+  em::cplx* d_twl[em::kLongMaxP1 + 1] = {};   // column twiddles per P1
   static constexpr int kLanes = 3;          // waves of long transforms run round-robin on these streams
   cudaStream_t lane[kLanes] = {};
   cudaEvent_t ev_fork = nullptr, ev_join[kLanes] = {};
@@ -255,10 +264,11 @@ int fft_group(bool blue, int log2p) {
 }
 
 // ===================================== long-line path ==========================================
+#define FOR_EACH_P1(M) M(3) M(4) M(5) M(6) M(7) M(8) M(10) M(12) M(14) M(16) M(20) M(24) M(28) M(32)
 #define FOR_EACH_LOG2P1(M) M(2) M(3) M(4) M(5)
 
 constexpr size_t kLongRowSmem = (em::padded_len<em::kLongLog2P2>() + em::stage_tw_total(em::kLongLog2P2)) * sizeof(em::cplx);
-inline size_t long_col_smem(int log2p1) { return ((size_t)1 << log2p1) * em::kLongColsPerCta * sizeof(em::cplx); }
+inline size_t long_col_smem(int p1) { return (size_t)p1 * em::kLongColsPerCta * sizeof(em::cplx); }
 constexpr int kLongColBlocks = em::kLongP2 / em::kLongColsPerCta;
 
 int init_long_attrs() {
@@ -267,39 +277,43 @@ int init_long_attrs() {
   CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));        \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));  \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));
-  FOR_EACH_LOG2P1(M)
+  FOR_EACH_P1(M)
 #undef M
+  // twiddles of the non-power-of-two column DFTs
+  std::vector<em::cplx> tw((size_t)(em::kLongMaxP1 + 1) * em::kLongMaxP1, em::cplx{0.0, 0.0});
+  const long double two_pi = 6.283185307179586476925286766559005768L;
+  for (int r = 1; r <= em::kLongMaxP1; ++r)
+    for (int m = 0; m < r; ++m) {
+      const long double ang = two_pi * (long double)m / (long double)r;
+      tw[(size_t)r * em::kLongMaxP1 + m] = em::cplx{(double)cosl(ang), (double)sinl(ang)};
+    }
+  CU_TRY(cudaMemcpyToSymbol(em::kDftTw, tw.data(), tw.size() * sizeof(em::cplx)));
   return PROTON_EM_OK;
 }
 
-// Transforms per wave: keep the P-point work buffers of a wave around half of the 126 MB L2.
-int long_wave_capacity(int log2p) {
+// Transforms per wave (PROTON_EM_LONG_WAVE_MB megabytes of work buffer per stream, default 32).
+int long_wave_capacity(int p1) {
   static long long budget_mb = [] {
     const char* e = std::getenv("PROTON_EM_LONG_WAVE_MB");
     const long long v = e ? std::atoll(e) : 0;
     return v > 0 ? v : 32LL;
   }();
-  const long long bytes = ((long long)1 << log2p) * (long long)sizeof(em::cplx);
+  const long long bytes = (long long)p1 * em::kLongP2 * (long long)sizeof(em::cplx);
   return (int)std::max<long long>(4, std::min<long long>(1024, (budget_mb << 20) / bytes));
 }
 
-int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long n_tr_total) {
-  const int lp1 = log2p - em::kLongLog2P2;
-  if (lp1 < kLongMinLog2P1 || lp1 > kLongMaxLog2P1) return fail(PROTON_EM_EINVAL, "bad long log2p %d", log2p);
-  if (!ctx->d_twl[lp1]) {
-    const size_t n = ((size_t)1 << lp1) * em::kLongP2;
-    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_twl[lp1]), n * sizeof(em::cplx)));
-    const int grid = (int)((n + 255) / 256);
-    switch (lp1) {
-#define M(q) case q: em::em_long_twiddle_kernel<q><<<grid, 256, 0, ctx->stream>>>(ctx->d_twl[lp1]); break;
-      FOR_EACH_LOG2P1(M)
-#undef M
-    }
+int ensure_long(proton_em_ctx* ctx, int p1, int cap, long long n_tr_total) {
+  if (p1 < 3 || p1 > em::kLongMaxP1) return fail(PROTON_EM_EINVAL, "bad long row count %d", p1);
+  if (!ctx->d_twl[p1]) {
+    const size_t n = (size_t)p1 * em::kLongP2;
+    CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_twl[p1]), n * sizeof(em::cplx)));
+    em::em_long_twiddle_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_twl[p1], p1);
     ctx->launches++;
     CU_TRY(cudaGetLastError());
+    CU_TRY(cudaStreamSynchronize(ctx->stream));     // the lanes read it without ordering against this stream
   }
   const size_t lanes = proton_em_ctx::kLanes;
-  const size_t need_x = lanes * ((size_t)cap << log2p);
+  const size_t need_x = lanes * (size_t)cap * (size_t)p1 * em::kLongP2;
   const size_t need_p = (size_t)std::max<long long>(n_tr_total, 1) * 2 * kLongColBlocks;
   if (ctx->long_x.n < need_x || ctx->long_part_v.n < need_p) {
     CU_TRY(cudaDeviceSynchronize());                // earlier waves may still use the old buffers
@@ -309,40 +323,43 @@ int ensure_long(proton_em_ctx* ctx, int log2p, int cap, long long n_tr_total) {
   return PROTON_EM_OK;
 }
 
-int launch_long_colfwd(proton_em_ctx* ctx, cudaStream_t st, int lp1, const em::ColParams& cp, int groups) {
+int launch_long_colfwd(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::ColParams& cp, int groups) {
   const dim3 grid(kLongColBlocks, groups);
-  switch (lp1) {
+  switch (p1) {
 #define M(q) case q: em::em_long_colfwd_kernel<q><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp); break;
-    FOR_EACH_LOG2P1(M)
+    FOR_EACH_P1(M)
 #undef M
+    default: return fail(PROTON_EM_EINVAL, "unsupported row count %d", p1);
   }
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   return PROTON_EM_OK;
 }
 
-int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int lp1, bool blue, const em::ColParams& cp, int groups) {
+int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int p1, bool blue, const em::ColParams& cp, int groups) {
   const dim3 grid(kLongColBlocks, groups);
-  switch (lp1) {
-#define M(q)                                                                                                        \
-  case q:                                                                                                           \
-    if (blue) em::em_long_colinv_kernel<q, true><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp);  \
-    else em::em_long_colinv_kernel<q, false><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp);      \
+  switch (p1) {
+#define M(q)                                                                                              \
+  case q:                                                                                                 \
+    if (blue) em::em_long_colinv_kernel<q, true><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp); \
+    else em::em_long_colinv_kernel<q, false><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp);     \
     break;
-    FOR_EACH_LOG2P1(M)
+    FOR_EACH_P1(M)
 #undef M
+    default: return fail(PROTON_EM_EINVAL, "unsupported row count %d", p1);
   }
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   return PROTON_EM_OK;
 }
 
-int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int lp1, const em::LongWave& w, int maxN) {
+int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::LongWave& w, int maxN) {
   const dim3 grid(std::min(256, (maxN + 255) / 256), w.n_tr);
-  switch (lp1) {
-#define M(q) case q: em::em_long_scatter_kernel<q><<<grid, 256, 0, st>>>(w); break;
+  switch (p1) {
+#define M(q) case (1 << q): em::em_long_scatter_kernel<q><<<grid, 256, 0, st>>>(w); break;
     FOR_EACH_LOG2P1(M)
 #undef M
+    default: return fail(PROTON_EM_EINVAL, "unsupported row count %d", p1);
   }
   ctx->launches++;
   CU_TRY(cudaGetLastError());
@@ -350,7 +367,7 @@ int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int lp1, const em::
 }
 
 int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp, int n_tr) {
-  const dim3 grid(1 << rp.log2p1, n_tr);
+  const dim3 grid(rp.p1, n_tr);
   em::em_long_row_kernel<<<grid, em::kLongRowThreads, kLongRowSmem, st>>>(rp);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
@@ -358,10 +375,9 @@ int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp
 }
 
 // pre / post chirps and the transformed chirp H of new long lengths (all entries share log2p and kind).
-int long_build_tables(proton_em_ctx* ctx, const std::vector<em::NTab>& entries, int log2p, bool blue) {
-  const int lp1 = log2p - em::kLongLog2P2;
-  const int cap = long_wave_capacity(log2p);
-  { int rc = ensure_long(ctx, log2p, cap, 1); if (rc) return rc; }
+int long_build_tables(proton_em_ctx* ctx, const std::vector<em::NTab>& entries, int lp1, bool blue) {
+  const int cap = long_wave_capacity(lp1);
+  { int rc = ensure_long(ctx, lp1, cap, 1); if (rc) return rc; }
   em::NTab* d_e = nullptr;
   CU_TRY(cudaMalloc(reinterpret_cast<void**>(&d_e), entries.size() * sizeof(em::NTab)));
   struct G { em::NTab* p; ~G() { cudaFree(p); } } g{d_e};
@@ -436,7 +452,8 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
     t.n = N;
     t.log2p = (c.cls == CLS_POW2 || c.cls == CLS_BLUE) ? c.log2p : 0;
     t.bluestein = c.cls == CLS_BLUE;
-    if (c.cls == CLS_LPOW2 || c.cls == CLS_LBLUE) { t.log2p = c.log2p; t.bluestein = c.cls == CLS_LBLUE; }
+    t.p1 = 0;
+    if (c.cls == CLS_LPOW2 || c.cls == CLS_LBLUE) { t.p1 = c.log2p; t.bluestein = c.cls == CLS_LBLUE; }
     if (c.cls != CLS_SMALL) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
@@ -446,7 +463,8 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
       t.post = static_cast<const em::cplx*>(p);
-      CU_TRY(ctx->arena.alloc(&p, ((size_t)1 << c.log2p) * sizeof(em::cplx)));
+      const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2 : ((size_t)1 << c.log2p);
+      CU_TRY(ctx->arena.alloc(&p, plen * sizeof(em::cplx)));
       t.hhat = static_cast<const em::cplx*>(p);
     }
     entries[i] = t;
@@ -471,12 +489,12 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
     }
   }
   for (int blue = 0; blue < 2; ++blue) {
-    for (int p = em::kLongLog2P2 + kLongMinLog2P1; p <= em::kLongLog2P2 + kLongMaxLog2P1; ++p) {
+    for (int p1 = 3; p1 <= em::kLongMaxP1; ++p1) {
       std::vector<em::NTab> grp;
       for (const em::NTab& t : entries)
-        if (t.log2p == p && t.bluestein == blue) grp.push_back(t);
+        if (t.p1 == p1 && t.bluestein == blue) grp.push_back(t);
       if (grp.empty()) continue;
-      int rc = long_build_tables(ctx, grp, p, blue != 0);
+      int rc = long_build_tables(ctx, grp, p1, blue != 0);
       if (rc) return rc;
     }
   }
@@ -818,7 +836,7 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
                            double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag, double critical) {
   proton_em_ctx* ctx = p->ctx;
   const bool blue = cl.cls == CLS_LBLUE;
-  const int lp1 = cl.log2p - em::kLongLog2P2;
+  const int lp1 = cl.log2p;          // P1 (rows of 4096 points) for the long classes
   const int npairs = (T + 1) / 2;
   const long long n_tr_total = (long long)cl.count * npairs;
   if (n_tr_total > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many long transforms");
@@ -847,7 +865,7 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
     const int cnt = (int)std::min<long long>(cap, n_tr_total - s0);
     const int li = wave % proton_em_ctx::kLanes;
     cudaStream_t st = ctx->lane[li];
-    em::cplx* xbuf = ctx->long_x.p + (size_t)li * ((size_t)cap << cl.log2p);
+    em::cplx* xbuf = ctx->long_x.p + (size_t)li * (size_t)cap * (size_t)lp1 * em::kLongP2;
     em::LongWave w{};
     w.tr_line = ctx->long_tr_line.p + s0; w.tr_pair = ctx->long_tr_pair.p + s0; w.n_tr = cnt; w.T = T;
     w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
