@@ -81,6 +81,24 @@ template <int R, int SIGN> struct DftAny {
   static __device__ __forceinline__ void run(cplx (&v)[R]) {
     if constexpr ((R & (R - 1)) == 0) {
       DftBig<R, SIGN>::run(v);
+    } else if constexpr (R % 2 == 0) {
+      // even length: one radix-2 split on top of two DFTs of length R/2
+      cplx e[R / 2], o[R / 2];
+#pragma unroll
+      for (int i = 0; i < R / 2; ++i) { e[i] = v[2 * i]; o[i] = v[2 * i + 1]; }
+      DftAny<R / 2, SIGN>::run(e);
+      DftAny<R / 2, SIGN>::run(o);
+#pragma unroll
+      for (int r = 0; r < R / 2; ++r) {
+        cplx t = o[r];
+        if (r != 0) {
+          const cplx w = kDftTw[R][r];
+          const double wy = SIGN > 0 ? w.y : -w.y;
+          t = cplx{fma(o[r].x, w.x, -(o[r].y * wy)), fma(o[r].x, wy, o[r].y * w.x)};
+        }
+        v[r] = cadd(e[r], t);
+        v[r + R / 2] = csub(e[r], t);
+      }
     } else {
       cplx y[R];
 #pragma unroll

@@ -58,7 +58,7 @@ constexpr int kMaxPow2N = 1 << kMaxLog2P;          // 8192
 constexpr int kMaxBlueN = (1 << (kMaxLog2P - 1));  // 4096: 2N-1 <= 8192
 
 // Long lines: P = P1 * 4096 with P1 from this list (any P1 works for Bluestein; powers of two for 2^p lines).
-constexpr int kLongP1List[] = {3, 4, 5, 6, 7, 8, 10, 12, 14, 16, 20, 24, 28, 32};
+constexpr int kLongP1List[] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32};
 constexpr int kMaxLongPow2N = em::kLongP2 * em::kLongMaxP1;                 // 131072
 constexpr int kMaxLongBlueN = (em::kLongP2 * em::kLongMaxP1) / 2;           // 65536: 2N-1 <= 131072
 
@@ -264,7 +264,7 @@ int fft_group(bool blue, int log2p) {
 }
 
 // ===================================== long-line path ==========================================
-#define FOR_EACH_P1(M) M(3) M(4) M(5) M(6) M(7) M(8) M(10) M(12) M(14) M(16) M(20) M(24) M(28) M(32)
+#define FOR_EACH_P1(M) M(3) M(4) M(5) M(6) M(7) M(8) M(9) M(10) M(11) M(12) M(13) M(14) M(15) M(16) M(18) M(20) M(22) M(24) M(26) M(28) M(30) M(32)
 #define FOR_EACH_LOG2P1(M) M(2) M(3) M(4) M(5)
 
 constexpr size_t kLongRowSmem = (em::padded_len<em::kLongLog2P2>() + em::stage_tw_total(em::kLongLog2P2)) * sizeof(em::cplx);
