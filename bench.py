@@ -83,7 +83,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.FIELDS}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -128,7 +128,7 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def cpu_baseline_port(batch, ts, budget_s=15.0):
+def cpu_baseline_port(batch, ts, budget_s=12.0):
     """The CPU oracle port (oracle/em_oracle.c, double-precision DCT, all host threads) on a bounded sample."""
     from oracle import restatement as R
     R.load()
@@ -144,11 +144,15 @@ def cpu_baseline_port(batch, ts, budget_s=15.0):
     want = rate * budget_s
     Tn = len(ts)
     stride = max(1, int(np.ceil(batch.total_nodes * Tn / want)))
-    sample = batch.subset(np.sort(order[::stride]))
-    t0 = time.perf_counter()
-    R.batch(sample.num_nodes, sample.a_coeff, sample.trip_off, sample.trip_row, sample.trip_col, sample.trip_val,
-            sample.u_off, sample.curden, ts, want_stress=False, use_double=True)
-    dt = time.perf_counter() - t0
+    for _ in range(2):
+        sample = batch.subset(np.sort(order[::stride]))
+        t0 = time.perf_counter()
+        R.batch(sample.num_nodes, sample.a_coeff, sample.trip_off, sample.trip_row, sample.trip_col, sample.trip_val,
+                sample.u_off, sample.curden, ts, want_stress=False, use_double=True)
+        dt = time.perf_counter() - t0
+        if stride == 1 or dt > budget_s / 3:
+            break
+        stride = max(1, int(stride * dt / budget_s * 1.2))      # the probe under-estimated the rate: enlarge once
     return {"value": sample.total_nodes * Tn / dt, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": f"every {stride}-th line by length ({sample.num_lines} lines, {sample.total_nodes} nodes) x {Tn} "
                       f"timestamps, {dt:.1f} s; oracle/em_oracle.c with the double-precision O(N log N) DCT, pthreads"}
@@ -172,7 +176,7 @@ def run_reference(args, world, rank):
         #  and a stride keeps each step to tens of seconds
         ok = np.nonzero(batch.num_nodes <= 8000)[0]
         order = ok[np.argsort(-batch.num_nodes[ok], kind="stable")]
-        sel = np.sort(order[:: max(1, len(order) // 160)])
+        sel = np.sort(order[:: max(1, len(order) // 600)])
         sub = batch.subset(sel)
         t_one = float(ts[-1])
         tmp = tempfile.mkdtemp(prefix="proton_ref_")
@@ -201,7 +205,7 @@ def run_reference(args, world, rank):
         dt = (time.perf_counter() - t0) / args.steps
         evals = sub.total_nodes
         kind = "reference"
-        sample = (f"{sub.num_lines} lines (every {max(1, len(order) // 160)}-th by length among N <= 8000; longer lines need "
+        sample = (f"{sub.num_lines} lines (every {max(1, len(order) // 600)}-th by length among N <= 8000; longer lines need "
                   f">0.5 GB each in the reference), {sub.total_nodes} nodes, 1 timestamp per process, {cores} worker threads; "
                   "bin/EMtool_analytical + shim FFT (MKL not on this box)")
     else:
@@ -219,7 +223,7 @@ def run_reference(args, world, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="ibmpg2_shaped")
@@ -365,7 +369,22 @@ def main():
         e2e = {"value": evals_total / dt, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                "ms_per_step": dt * 1e3, "steps": n_e2e,
                "note": "proton_em_analyze_host through ctypes: pack + H2D + eval + D2H of the full stress field "
-                       "into pinned host memory, wall clock"}
+                       "into pinned host memory, wall clock; bounded by PCIe (8 B per eval)"}
+        # the whole-grid `analyze` use case consumes only max / argmax / flag per (line, t) (PROTON_cli.py:1058-1066)
+        out2 = EvalResult(None, h_mx.numpy(), h_amx.numpy(), h_flag.numpy(), hb.node_off, T)
+        ctx.analyze_host(hb, h_ts, critical=CRITICAL, want_stress=False, out=out2)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            ctx.analyze_host(hb, h_ts, critical=CRITICAL, want_stress=False, out=out2)
+        dt2 = (time.perf_counter() - t0) / n_e2e
+        if world > 1:
+            tm = torch.tensor([dt2], device=dev, dtype=torch.float64)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            dt2 = float(tm.item())
+        e2e["reduce_only"] = {"value": evals_total / dt2, "unit": UNIT, "ms_per_step": dt2 * 1e3,
+                              "d2h_bytes_per_step": int(L * T * 13),
+                              "note": "same call with stress == NULL: only max / argmax / flag come back"}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
