@@ -9,6 +9,7 @@
 #include "../../include/proton_em.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -30,6 +31,19 @@
 namespace {
 
 thread_local std::string g_last_error;
+
+struct Trace {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  const char* what;
+  explicit Trace(const char* w) : on(std::getenv("PROTON_EM_TRACE") != nullptr), t0(std::chrono::steady_clock::now()), what(w) {}
+  void lap(const char* label) {
+    if (!on) return;
+    const auto t1 = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[proton_em] %s: %s %.3f ms\n", what, label, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
 
 int fail(int code, const char* fmt, ...) {
   char buf[1024];
@@ -188,6 +202,7 @@ struct proton_em_plan {
   // that the device-to-host copy of one chunk overlaps the evaluation of the next).
   struct Chunk { int64_t l0, l1; std::vector<ClassList> classes; };
   std::vector<Chunk> chunks;
+  std::vector<int> h_class_lines;    // host copy of d_class_lines
   std::vector<long long> node_off;   // host copy
   std::vector<int> num_nodes;        // host copy
 };
@@ -657,6 +672,7 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
   if (L > 0 && (!b->num_nodes || !b->a_coeff || !b->trip_off || !b->u_off))
     return fail(PROTON_EM_EINVAL, "proton_em_pack: NULL batch array");
   { int rc = set_device(ctx); if (rc) return rc; }
+  Trace tr("pack");
   proton_em_plan* p = new proton_em_plan();
   p->ctx = ctx;
   p->L = L;
@@ -701,7 +717,9 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
     if (classify(N).cls == CLS_NONE)
       return fail(PROTON_EM_EINVAL, "a line has %d nodes; this build handles N <= %d (any N) and powers of two up to %d",
                   N, kMaxLongBlueN, kMaxLongPow2N);
+  tr.lap("sizes");
   { int rc = ensure_tables(ctx, distinct); if (rc) return rc; }
+  tr.lap("ensure_tables");
   std::unordered_map<int, int> tab_index;
   std::vector<em::NTab> tabs(distinct.size());
   for (size_t i = 0; i < distinct.size(); ++i) { tabs[i] = ctx->tabs[distinct[i]]; tab_index[distinct[i]] = (int)i; }
@@ -741,6 +759,7 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
     }
   }
 
+  tr.lap("class lists");
   // ---- device copies -----------------------------------------------------------------------
   cudaStream_t st = ctx->stream;
   DevBuf<int> tmp_row, tmp_col, tmp_perm;
@@ -802,8 +821,10 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
   CU_TRY(cudaMemcpyAsync(p->d_line_tab.p, line_tab.data(), L * sizeof(int), cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(p->d_tabs.p, tabs.data(), tabs.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, st));
   CU_TRY(cudaMemcpyAsync(p->d_class_lines.p, class_lines.data(), class_lines.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+  p->h_class_lines = class_lines;
   CU_TRY(cudaMemsetAsync(d_err.p, 0, sizeof(int), st));
 
+  tr.lap("allocs + uploads queued");
   // ---- (a) packing kernel, (b) forward DCT kernel ------------------------------------------
   em::PackParams pp{L, p->d_num_nodes, p->d_trip_off, d_row, d_col, d_val, d_u_off, d_u,
                     tmp_perm.p, tmp_prod.p, p->d_r_idx.p, p->d_r_val.p, p->d_r_cnt.p, d_err.p};
@@ -825,6 +846,7 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
   int err = 0;
   CU_TRY(cudaMemcpyAsync(&err, d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
+  tr.lap("kernels + sync");
   if (err != 0)
     return fail(PROTON_EM_EINVAL, "line %d: a B triplet has a row outside [0, num_nodes) or a column outside [0, #curden)", err - 1);
   guard.p = nullptr;
@@ -832,26 +854,34 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
   return PROTON_EM_OK;
 }
 
-static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& cl, const double* d_ts, int T,
-                           double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag, double critical) {
+// All long classes of a chunk: their transforms are listed once, cut into waves per class, and the waves are dealt
+// round-robin to the lanes (streams) so that small waves of different classes overlap; one join, one reduction.
+static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_plan::ClassList*>& longs,
+                         const double* d_ts, int T, double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag,
+                         double critical) {
   proton_em_ctx* ctx = p->ctx;
-  const bool blue = cl.cls == CLS_LBLUE;
-  const int lp1 = cl.log2p;          // P1 (rows of 4096 points) for the long classes
   const int npairs = (T + 1) / 2;
-  const long long n_tr_total = (long long)cl.count * npairs;
+  long long n_tr_total = 0;
+  for (const auto* cl : longs) n_tr_total += (long long)cl->count * npairs;
   if (n_tr_total > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many long transforms");
-  // class lines are sorted longest first
-  std::vector<int> lines(cl.count);
-  CU_TRY(cudaMemcpy(lines.data(), p->d_class_lines.p + cl.offset, cl.count * sizeof(int), cudaMemcpyDeviceToHost));
-  int maxN = 0;
-  for (int l : lines) maxN = std::max(maxN, p->num_nodes[l]);
-  const int cap = (int)std::min<long long>(long_wave_capacity(cl.log2p), n_tr_total);
-  { int rc = ensure_long(ctx, cl.log2p, cap, n_tr_total); if (rc) return rc; }
+  int max_cap_p1 = 0;
+  for (const auto* cl : longs) {
+    const int cap = (int)std::min<long long>(long_wave_capacity(cl->log2p), (long long)cl->count * npairs);
+    int rc = ensure_long(ctx, cl->log2p, cap, n_tr_total);
+    if (rc) return rc;
+    max_cap_p1 = std::max(max_cap_p1, cap * cl->log2p);
+  }
   std::vector<int> tr_line((size_t)n_tr_total), tr_pair((size_t)n_tr_total);
-  for (int i = 0; i < cl.count; ++i)
-    for (int pr = 0; pr < npairs; ++pr) { tr_line[(size_t)i * npairs + pr] = lines[i]; tr_pair[(size_t)i * npairs + pr] = pr; }
+  {
+    size_t o = 0;
+    for (const auto* cl : longs)
+      for (int i = 0; i < cl->count; ++i) {
+        const int line = p->h_class_lines[cl->offset + i];
+        for (int pr = 0; pr < npairs; ++pr, ++o) { tr_line[o] = line; tr_pair[o] = pr; }
+      }
+  }
   if (ctx->long_tr_line.n < (size_t)n_tr_total) {
-    CU_TRY(cudaStreamSynchronize(ctx->stream));
+    CU_TRY(cudaDeviceSynchronize());
     CU_TRY(ctx->long_tr_line.alloc((size_t)n_tr_total));
     CU_TRY(ctx->long_tr_pair.alloc((size_t)n_tr_total));
   }
@@ -860,40 +890,51 @@ static int eval_long_class(proton_em_plan* p, const proton_em_plan::ClassList& c
   // fork: the lanes start after everything queued so far on the main stream (uploads above included)
   CU_TRY(cudaEventRecord(ctx->ev_fork, ctx->stream));
   for (int i = 0; i < proton_em_ctx::kLanes; ++i) CU_TRY(cudaStreamWaitEvent(ctx->lane[i], ctx->ev_fork, 0));
+  const size_t lane_stride = ctx->long_x.n / proton_em_ctx::kLanes;     // complex elements per lane
   int wave = 0;
-  for (long long s0 = 0; s0 < n_tr_total; s0 += cap, ++wave) {
-    const int cnt = (int)std::min<long long>(cap, n_tr_total - s0);
-    const int li = wave % proton_em_ctx::kLanes;
-    cudaStream_t st = ctx->lane[li];
-    em::cplx* xbuf = ctx->long_x.p + (size_t)li * (size_t)cap * (size_t)lp1 * em::kLongP2;
-    em::LongWave w{};
-    w.tr_line = ctx->long_tr_line.p + s0; w.tr_pair = ctx->long_tr_pair.p + s0; w.n_tr = cnt; w.T = T;
-    w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
-    w.tabs = p->d_tabs.p; w.W = p->d_W.p; w.ts = d_ts; w.exp_tab = ctx->d_exp;
-    w.x = xbuf; w.stress = d_stress; w.tr_base = (int)s0;
-    w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p;
-    w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
-    w.critical = critical;
-    const int tpc = std::max(1, cnt / 24);
-    const int groups = (cnt + tpc - 1) / tpc;
-    em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
-    em::RowParams rp{xbuf, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
-                     ctx->d_tw[em::kLongLog2P2]};
-    int rc;
-    if (blue) rc = launch_long_colfwd(ctx, st, lp1, cp, groups);
-    else rc = launch_long_scatter(ctx, st, lp1, w, maxN);
-    if (rc) return rc;
-    rc = launch_long_row(ctx, st, rp, cnt);
-    if (rc) return rc;
-    rc = launch_long_colinv(ctx, st, lp1, blue, cp, groups);
-    if (rc) return rc;
+  long long base = 0;
+  for (const auto* cl : longs) {
+    const bool blue = cl->cls == CLS_LBLUE;
+    const int lp1 = cl->log2p;          // P1 (rows of 4096 points) for the long classes
+    const long long n_tr = (long long)cl->count * npairs;
+    const int cap = (int)std::min<long long>(long_wave_capacity(lp1), n_tr);
+    int maxN = 0;
+    for (int i = 0; i < cl->count; ++i) maxN = std::max(maxN, p->num_nodes[p->h_class_lines[cl->offset + i]]);
+    for (long long s0 = 0; s0 < n_tr; s0 += cap, ++wave) {
+      const int cnt = (int)std::min<long long>(cap, n_tr - s0);
+      const int li = wave % proton_em_ctx::kLanes;
+      cudaStream_t st = ctx->lane[li];
+      em::cplx* xbuf = ctx->long_x.p + (size_t)li * lane_stride;
+      em::LongWave w{};
+      w.tr_line = ctx->long_tr_line.p + base + s0; w.tr_pair = ctx->long_tr_pair.p + base + s0; w.n_tr = cnt; w.T = T;
+      w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
+      w.tabs = p->d_tabs.p; w.W = p->d_W.p; w.ts = d_ts; w.exp_tab = ctx->d_exp;
+      w.x = xbuf; w.stress = d_stress; w.tr_base = (int)(base + s0);
+      w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p;
+      w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
+      w.critical = critical;
+      const int tpc = std::max(1, cnt / 24);
+      const int groups = (cnt + tpc - 1) / tpc;
+      em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
+      em::RowParams rp{xbuf, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
+                       ctx->d_tw[em::kLongLog2P2]};
+      int rc;
+      if (blue) rc = launch_long_colfwd(ctx, st, lp1, cp, groups);
+      else rc = launch_long_scatter(ctx, st, lp1, w, maxN);
+      if (rc) return rc;
+      rc = launch_long_row(ctx, st, rp, cnt);
+      if (rc) return rc;
+      rc = launch_long_colinv(ctx, st, lp1, blue, cp, groups);
+      if (rc) return rc;
+    }
+    base += n_tr;
   }
-  // join: later work on the main stream (next class, caller's copies) waits for every lane
+  // join: later work on the main stream waits for every lane
   for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
     CU_TRY(cudaEventRecord(ctx->ev_join[i], ctx->lane[i]));
     CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0));
   }
-  {   // one reduction of the column-block partials for the whole class
+  {   // one reduction of the column-block partials for all long transforms of the chunk
     em::LongWave w{};
     w.tr_line = ctx->long_tr_line.p; w.tr_pair = ctx->long_tr_pair.p; w.n_tr = (int)n_tr_total; w.T = T;
     w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
@@ -924,6 +965,15 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
   if (alg != PROTON_EM_ALG_AUTO) return fail(PROTON_EM_EINVAL, "unknown algorithm %d", alg);
   const long long target_items = (long long)ctx->sm_count * 12;
   if (chunk_end < 0) chunk_end = (int)p->chunks.size();
+  std::vector<const proton_em_plan::ClassList*> longs;
+  for (int ci = chunk_begin; ci < chunk_end; ++ci)
+    for (const auto& cl : p->chunks[ci].classes)
+      if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) longs.push_back(&cl);
+  // long lines first: their waves run on the lanes while the main stream works through the other classes
+  if (!longs.empty()) {
+    int rc = eval_long_all(p, longs, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical);
+    if (rc) return rc;
+  }
   for (int ci = chunk_begin; ci < chunk_end; ++ci)
   for (const auto& cl : p->chunks[ci].classes) {
     if (cl.cls == CLS_SMALL) {
@@ -939,11 +989,7 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
       CU_TRY(cudaGetLastError());
       continue;
     }
-    if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) {
-      int rc = eval_long_class(p, cl, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical);
-      if (rc) return rc;
-      continue;
-    }
+    if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) continue;
     const bool blue = cl.cls == CLS_BLUE;
     const int G = fft_group(blue, cl.log2p);
     const int npairs = (T + 1) / 2;
@@ -1007,9 +1053,11 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const d
   int64_t chunk_bytes = chunk_mb << 20;
   if (max_device_bytes > 0) chunk_bytes = std::min<int64_t>(chunk_bytes, std::max<int64_t>(max_device_bytes / 2, 1 << 20));
   const int64_t chunk_nodes = res->stress ? std::max<int64_t>(1, chunk_bytes / (8 * (int64_t)T)) : 0;
+  Trace tr("analyze_host");
   proton_em_plan* plan = nullptr;
   { int rc = pack_impl(ctx, b, PROTON_EM_HOST, chunk_nodes, &plan); if (rc) return rc; }
-  struct PG { proton_em_plan* p; ~PG() { destroy_plan(p); } } pg{plan};
+  struct PG { proton_em_plan* p; ~PG() { Trace t2("analyze_host"); destroy_plan(p); t2.lap("destroy_plan"); } } pg{plan};
+  tr.lap("pack");
   const int64_t L = plan->L;
   const size_t LT = (size_t)L * T;
   int64_t max_nodes = 0;
@@ -1042,11 +1090,14 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const d
     }
   }
   if (rc) { cudaDeviceSynchronize(); return rc; }
+  tr.lap("evals queued");
   CU_TRY(cudaMemcpyAsync(res->max_stress, ctx->io_mx.p, LT * sizeof(double), cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaMemcpyAsync(res->argmax, ctx->io_amx.p, LT * sizeof(int), cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaMemcpyAsync(res->flag, ctx->io_flag.p, LT * sizeof(unsigned char), cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
+  tr.lap("main stream done");
   CU_TRY(cudaStreamSynchronize(cs));
+  tr.lap("copy stream done");
   return PROTON_EM_OK;
 }
 
