@@ -1,0 +1,134 @@
+"""Whole-grid EM check: the batched twin of PROTON's `analyze <t> --critical s --sample k` command.
+
+The reference walks `<project>/<benchmark>/**/<layer>_<net>_<k>.csv`, and per line (one thread + one process each)
+discretises with dx = 0.99 x the shortest segment, runs the analytical kernel, re-reads the stress file, takes the
+maximum and compares it with the critical stress (PROTON_cli.py:992-1073, :1076-1214).  Here the same lines are
+formulated in memory (proton_b200.formulation), packed once and evaluated in ONE batched GPU call; the per-line maxima
+and flags come straight from the fused epilogue.  Optionally the reference's on-disk outputs
+(`output/<line>/<tech>_<T>_<W>/stress_<%f>.txt`, one `%.18g` per line) are written so that `report_line_stress`, the
+GUI's `add_plot` and `export_function` keep working.
+
+The reference sets a module-global discretisation step from many pool threads (a race); here dx is a
+local of each line, so results are deterministic.
+"""
+from __future__ import annotations
+
+import os
+import random
+import time
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import formulation as F
+from .api import Context, LineBatch
+
+
+@dataclass
+class AnalyzeReport:
+    lines: List[str]
+    discarded: Dict[str, str]                 # line -> reason (reference prints "The line was discarded")
+    max_stress: np.ndarray                    # [L, T]
+    argmax: np.ndarray                        # [L, T]
+    flag: np.ndarray                          # [L, T]
+    problematic_lines: Dict[str, float]       # line -> max stress at the LAST timestamp, if above critical
+    seconds: float
+    timestamps: np.ndarray = field(default_factory=lambda: np.zeros(0))
+
+    @property
+    def max_stress_line(self) -> Optional[str]:
+        """The reference's final report: the line with the largest stress (PROTON_cli.py:1197-1213)."""
+        if not self.problematic_lines:
+            return None
+        return max(self.problematic_lines, key=self.problematic_lines.get)
+
+    def message(self) -> str:
+        return (f"EM stress analysis of {len(self.lines)} lines was successfully performed in {self.seconds:.3f} seconds; "
+                f"{len(self.problematic_lines)} line(s) exceed the critical stress.")
+
+
+def find_line_csvs(benchmark_dir: str) -> List[str]:
+    """`<benchmark>/<layer>/<layer>_<net>_<k>.csv` (spice_function_cli.py:253-263), sorted for determinism."""
+    out = []
+    for root, _dirs, files in os.walk(benchmark_dir):
+        for f in files:
+            if f.endswith(".csv"):
+                out.append(os.path.join(root, f))
+    return sorted(out)
+
+
+def formulate_for_analyze(csv_files: Sequence[str], technology: str, temperature: float, width: float):
+    """dx policy of analyze_line_item: step = 0.99 * min length, up to 10 retries with min length * 0.7."""
+    lines, discarded = [], {}
+    for path in csv_files:
+        name = os.path.splitext(os.path.basename(path))[0]
+        try:
+            segs, nlines = F.parse_line_csv(path)
+            if not segs:
+                discarded[name] = F.CORRUPT_MSG
+                continue
+            min_length = min(float(s[2]) for s in segs)
+            li = None
+            for _ in range(10):
+                try:
+                    li = F.formulate_segments(segs, sp_step=min_length * 0.99, technology=technology,
+                                              temperature=temperature, givenWidth=width, name=name, n_file_lines=nlines)
+                    break
+                except F.FormulationError as e:
+                    if str(e) != F.NOT_DENSE_MSG:
+                        raise
+                    min_length *= 0.7
+                    if min_length <= 0:
+                        break
+            if li is None:
+                discarded[name] = "The line was discarded"
+            else:
+                lines.append(li)
+        except (F.FormulationError, IndexError) as e:
+            discarded[name] = str(e)
+    return lines, discarded
+
+
+def write_reference_outputs(project_dir: str, lines, result, timestamps, technology, temperature, width) -> int:
+    """stress_<%f>.txt per (line, t) exactly where and how the reference binary writes them."""
+    n = 0
+    for l, li in enumerate(lines):
+        out_dir = os.path.join(project_dir, "output", li.name, f"{technology}_{temperature}_{width}")
+        os.makedirs(out_dir, exist_ok=True)
+        block = result.line(l)
+        for j, t in enumerate(timestamps):
+            with open(os.path.join(out_dir, "stress_" + ("%f" % float(t)) + ".txt"), "w") as f:
+                f.write("".join("%.18g\n" % v for v in block[j]))
+            n += 1
+    return n
+
+
+def analyze(project_dir: str, benchmark: str, simulation_time, critical_stress: Optional[float] = None,
+            sample_lines: Optional[int] = None, technology: str = "CuDD", temperature: float = 378.0, width: float = 0.1,
+            write_outputs: bool = False, ctx: Optional[Context] = None, seed: Optional[int] = None) -> AnalyzeReport:
+    """`simulation_time` may be one time (the reference's form) or a sequence of timestamps (seconds)."""
+    t0 = time.time()
+    ts = np.atleast_1d(np.asarray(simulation_time, dtype=np.float64))
+    csvs = find_line_csvs(os.path.join(project_dir, benchmark))
+    if sample_lines is not None and sample_lines < len(csvs):
+        rnd = random.Random(seed)
+        csvs = rnd.sample(csvs, sample_lines)          # PROTON_cli.py:1146-1149
+    lines, discarded = formulate_for_analyze(csvs, technology, float(temperature), float(width))
+    own = ctx is None
+    ctx = ctx or Context(0)
+    try:
+        batch = LineBatch.from_lines(lines)
+        res = ctx.analyze_host(batch, ts, critical=critical_stress, want_stress=write_outputs)
+    finally:
+        if own:
+            ctx.close()
+    if write_outputs:
+        write_reference_outputs(project_dir, lines, res, ts, technology, float(temperature), float(width))
+    problematic = {}
+    if critical_stress is not None:
+        for l, li in enumerate(lines):
+            if res.flag[l, -1]:
+                problematic[li.name] = float(res.max_stress[l, -1])
+    return AnalyzeReport([li.name for li in lines], discarded, res.max_stress, res.argmax, res.flag, problematic,
+                         time.time() - t0, ts)

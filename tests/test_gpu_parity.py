@@ -259,3 +259,43 @@ def test_launcher_writes_the_reference_output_file(oracle, tmp_path):
         if oracle.ref_binary_available() and N <= 2000:
             ref = oracle.reference_binary_line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, t)
             assert np.abs(got - ref).max() <= 1e-9 * np.abs(ref).max()
+
+
+def test_batched_analyze_driver_and_launcher_class(ctx, oracle, ibmpg1_lines, tmp_path):
+    """the batch-aware `analyze` (project directory in, problematic lines out, reference-format
+    stress files on request) and the in-process `Analytical_Class`."""
+    from proton_b200 import formulation as F
+    from proton_b200.analyze import analyze
+    from proton_b200.analytical import Analytical_Class
+    names, texts = ibmpg1_lines
+    proj = tmp_path / "proj"
+    picked = [i for i, n in enumerate(names) if n.startswith("M5_n1_")][:40]
+    for i in picked:
+        d = proj / "ibmpg1" / "M5"
+        d.mkdir(parents=True, exist_ok=True)
+        (d / f"{names[i]}.csv").write_text(texts[i])
+    rep = analyze(str(proj), "ibmpg1", [1e7, 6.38e8], critical_stress=40e6, write_outputs=True, ctx=ctx)
+    assert len(rep.lines) == len(picked) and "seconds" in rep.message()
+    for l, name in enumerate(rep.lines):
+        segs, _ = F.parse_line_csv(str(proj / "ibmpg1" / "M5" / f"{name}.csv"))
+        li = F.formulate_segments(segs, sp_step=F.analyze_policy_step(segs), name=name)
+        want, wm, _ = oracle.line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, [1e7, 6.38e8])
+        scale = np.abs(want).max(axis=1)
+        assert np.all(np.abs(rep.max_stress[l] - wm) <= 1e-9 * scale + 1e-300)
+        out = proj / "output" / name / "CuDD_378.0_0.1" / "stress_638000000.000000.txt"
+        got = np.array([float(x) for x in out.read_text().split()])
+        assert np.abs(got - want[1]).max() <= 1e-9 * scale[1] + 1e-300
+        assert (name in rep.problematic_lines) == bool(wm[1] > 40e6) or abs(wm[1] - 40e6) <= 1e-9 * scale[1]
+    # the reference's own two-step flow for one line: formulation files -> Analytical_Class
+    name = rep.lines[0]
+    segs, _ = F.parse_line_csv(str(proj / "ibmpg1" / "M5" / f"{name}.csv"))
+    li = F.formulate_segments(segs, given_disc_point=200, name=name)
+    d = proj / "input" / name / "CuDD_378.0_0.1"
+    oracle.write_line_inputs(d, li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, 6.38e8)
+    (d / "analytical.txt").write_text(f"nx_total = {li.num_nodes}\nAcoef = {li.a_coeff}\n")
+    msg = Analytical_Class(6.38e8, str(proj), name, "CuDD", 378.0, 0.1, ctx=ctx).analytical_function()
+    assert "seconds" in msg
+    got = np.array([float(x) for x in (proj / "output" / name / "CuDD_378.0_0.1" / "stress_638000000.000000.txt").read_text().split()])
+    want, _, _ = oracle.line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, [6.38e8])
+    assert len(got) == li.num_nodes and np.abs(got - want[0]).max() <= 1e-9 * np.abs(want[0]).max()
+    assert "No discretization" in Analytical_Class(1e6, str(proj), "nope", "CuDD", 378.0, 0.1, ctx=ctx).analytical_function()
