@@ -141,6 +141,9 @@ int proton_em_eval_line_noalloc(int device, void* stream, int32_t num_nodes, dou
 
 /* Test hook: y[i] = the device exp() used by the modal evaluation (must equal the host libm's). */
 int proton_em_debug_exp(proton_em_ctx* ctx, const double* x_host, double* y_host, int64_t n);
+/* Test hook: y[i] = exp(x[i]) - 1.0 exactly as the fused kernels evaluate the modal factor: bit-identical to the
+ * host libm's exp(x) - 1.0 where the reference cancels (|x| < ln2/256), within 2 ulp of exp elsewhere. */
+int proton_em_debug_expm1(proton_em_ctx* ctx, const double* x_host, double* y_host, int64_t n);
 
 #ifdef __cplusplus
 }

@@ -46,7 +46,7 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_plan_destroy", "proton_em_plan_total_nodes", "proton_em_plan_num_lines",
            "proton_em_plan_scratch_bytes", "proton_em_eval", "proton_em_synchronize", "proton_em_stream",
            "proton_em_launch_count", "proton_em_analyze_host", "proton_em_run_cfg", "proton_em_debug_exp",
-           "proton_em_eval_line_noalloc"]
+           "proton_em_eval_line_noalloc", "proton_em_debug_expm1"]
 
 
 def load() -> ctypes.CDLL:
@@ -76,6 +76,7 @@ def load() -> ctypes.CDLL:
                                            ctypes.POINTER(Result), ctypes.c_int64]
     lib.proton_em_run_cfg.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t]
     lib.proton_em_debug_exp.argtypes = [vp, vp, vp, ctypes.c_int64]
+    lib.proton_em_debug_expm1.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_eval_line_noalloc.argtypes = [ctypes.c_int, vp, ctypes.c_int32, ctypes.c_double, ctypes.c_int32, vp, vp,
                                                 vp, ctypes.c_int32, vp, vp, ctypes.c_int32, ctypes.c_double, vp, vp, vp, vp]
     _lib = lib

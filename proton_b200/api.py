@@ -184,6 +184,12 @@ class Context:
         check(self._lib.proton_em_debug_exp(self._h, x.ctypes.data, y.ctypes.data, x.size))
         return y
 
+    def debug_expm1(self, x) -> np.ndarray:
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.empty_like(x)
+        check(self._lib.proton_em_debug_expm1(self._h, x.ctypes.data, y.ctypes.data, x.size))
+        return y
+
     def run_cfg(self, cfg_path: str):
         """The reference process for one analytical.cfg -> (return code, stdout text of the reference)."""
         buf = ctypes.create_string_buffer(2048)

@@ -401,4 +401,10 @@ __global__ void em_exp_probe_kernel(const double* x, double* y, long long n, con
     y[i] = em_exp(x[i], exp_tab);
 }
 
+// exp(x) - 1.0 as the fused kernels evaluate it (em_expm1_ref), for the parity test of the modal factor.
+__global__ void em_expm1_probe_kernel(const double* x, double* y, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    y[i] = em_expm1_ref(x[i]);
+}
+
 }  // namespace em

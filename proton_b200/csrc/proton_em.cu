@@ -1101,7 +1101,12 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const d
   return PROTON_EM_OK;
 }
 
-int proton_em_debug_exp(proton_em_ctx* ctx, const double* x, double* y, int64_t n) {
+static int debug_exp_impl(proton_em_ctx* ctx, const double* x, double* y, int64_t n, int which);
+
+int proton_em_debug_exp(proton_em_ctx* ctx, const double* x, double* y, int64_t n) { return debug_exp_impl(ctx, x, y, n, 0); }
+int proton_em_debug_expm1(proton_em_ctx* ctx, const double* x, double* y, int64_t n) { return debug_exp_impl(ctx, x, y, n, 1); }
+
+static int debug_exp_impl(proton_em_ctx* ctx, const double* x, double* y, int64_t n, int which) {
   if (!ctx || !x || !y || n < 0) return fail(PROTON_EM_EINVAL, "proton_em_debug_exp: bad argument");
   if (n == 0) return PROTON_EM_OK;
   { int rc = set_device(ctx); if (rc) return rc; }
@@ -1109,7 +1114,8 @@ int proton_em_debug_exp(proton_em_ctx* ctx, const double* x, double* y, int64_t 
   struct G3 { DevBuf<double>&a, &b; ~G3() { a.free(); b.free(); } } g3{dx, dy};
   CU_TRY(dx.alloc(n)); CU_TRY(dy.alloc(n));
   CU_TRY(cudaMemcpyAsync(dx.p, x, n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-  em::em_exp_probe_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(dx.p, dy.p, n, ctx->d_exp);
+  if (which == 0) em::em_exp_probe_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(dx.p, dy.p, n, ctx->d_exp);
+  else em::em_expm1_probe_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(dx.p, dy.p, n);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   CU_TRY(cudaMemcpyAsync(y, dy.p, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));

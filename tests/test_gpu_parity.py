@@ -34,6 +34,27 @@ def test_device_exp_equals_host_libm_bit_for_bit(ctx, oracle):
     assert np.isnan(ctx.debug_exp(np.array([np.nan]))[0])
 
 
+def test_modal_factor_exp_minus_one(ctx, oracle):
+    """The fused kernels use em_expm1_ref: where the reference's exp(x) - 1.0 cancels (glibc's k == 0 branch,
+    |x| < ln2/256) it must return the SAME BITS as the host libm; elsewhere exp may be off by <= 2 ulp, which the
+    cancellation amplifies by at most 1/|x| <= 370 (1e-13 relative, four orders below the parity bound)."""
+    rng = np.random.default_rng(2)
+    small = -np.exp(rng.uniform(np.log(1e-18), np.log(0.0027), 2_000_000))
+    got = ctx.debug_expm1(small)
+    want = oracle.libm_exp(small) - 1.0
+    same = got.view(np.uint64) == want.view(np.uint64)
+    assert same.all(), f"{(~same).sum()} of {len(small)} differ in the cancellation regime"
+    big = np.concatenate([-np.exp(rng.uniform(np.log(0.0028), np.log(700.0), 2_000_000)), rng.uniform(-50, 0, 500_000),
+                          np.array([-708.0, -709.5, -745.0, -1e4, -np.inf, -0.0027076, -0.00271, -0.3465, -0.3466])])
+    got = ctx.debug_expm1(big)
+    e = oracle.libm_exp(big)
+    err = np.abs((got + 1.0) - e) / np.maximum(np.spacing(e), 1e-300)
+    rel = np.abs(got - (e - 1.0)) / np.abs(e - 1.0)
+    assert rel.max() <= 1e-13, rel.max()
+    assert np.isnan(ctx.debug_expm1(np.array([np.nan]))[0])
+    assert ctx.debug_expm1(np.array([0.0]))[0] == 0.0
+
+
 def _golden_batch(g, idx):
     from proton_b200.api import LineBatch
     tl = [g["trip_off"][i + 1] - g["trip_off"][i] for i in idx]
