@@ -254,6 +254,93 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const C
   }
 }
 
+// Forward column pass for the evaluation (mode 0) with every modal factor evaluated ONCE: entry k of the packed
+// spectrum needs the modal values of k and of its mirror N-k, which lives in column (N mod 4096) - j.  A CTA therefore
+// owns 64 column PAIRS {j, mirror(j)} (threads 0..63 one side, 64..127 the other), each thread evaluates only its own
+// modes and the two sides swap through shared memory.  Slot a pairs columns c/2 + a and c/2 - a (c = N mod 4096; for
+// even c the two self-mirrored columns c/2 and c/2 + 2048 stand alone), so the grid has 33 blocks of 64 slots.
+constexpr int kLongPairBlocks = kLongP2 / 128 + 1;
+
+template <int P1>
+__global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColParams p) {
+  constexpr int P2 = kLongP2, QMAX = (P1 + 1) / 2 + 1;
+  constexpr long long P = (long long)P1 * P2;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][128]   w_P^{-j r} of this thread's column
+  cplx* ys = twt + P1 * 128;                              // [QMAX][128] modal pairs (Yhat1, Yhat2) of this thread's modes
+  const int tid = threadIdx.x;
+  const int a = blockIdx.x * 64 + (tid & 63);
+  const int side = tid >> 6;
+  int prev_c = -1, j = 0, partner = tid;
+  bool active = false;
+  const int s0 = blockIdx.y * p.tr_per_cta;
+  const int s1 = min(p.w.n_tr, s0 + p.tr_per_cta);
+  for (int s = s0; s < s1; ++s) {
+    const int line = p.w.tr_line[s], pr = p.w.tr_pair[s];
+    const int N = p.w.num_nodes[line];
+    const int c = N & (P2 - 1);
+    if (c != prev_c) {
+      prev_c = c;
+      if (c & 1) {
+        active = a < P2 / 2;
+        j = side == 0 ? ((c + 1) / 2 + a) & (P2 - 1) : ((c - 1) / 2 - a) & (P2 - 1);
+        partner = tid ^ 64;
+      } else {
+        const bool self = (a == 0) || (a == P2 / 2);
+        active = a <= P2 / 2 && !(self && side == 1);
+        j = side == 0 ? (c / 2 + a) & (P2 - 1) : (c / 2 - a) & (P2 - 1);
+        partner = self ? tid : (tid ^ 64);
+      }
+      if (active)
+        for (int r = 1; r < P1; ++r) {
+          const cplx t = ldg_cplx(p.twl + (long long)r * P2 + j);
+          twt[r * 128 + tid] = cplx{t.x, -t.y};
+        }
+    }
+    const NTab tab = p.w.tabs[p.w.line_tab[line]];
+    const double* W = p.w.W + p.w.node_off[line];
+    const double av = p.w.a_coeff[line];
+    const double t1 = p.w.ts[2 * pr];
+    const double t2 = (2 * pr + 1 < p.w.T) ? p.w.ts[2 * pr + 1] : t1;
+    const double w1 = __dmul_rn(av, t1), w2 = __dmul_rn(av, t2);
+    cplx yk[QMAX];
+#pragma unroll
+    for (int q = 0; q < QMAX; ++q) {
+      const int k = j + q * P2;
+      yk[q] = cplx{0.0, 0.0};
+      if (active && q < P1 && k < N) {
+        const double l = tab.lam[k], wk = W[k];
+        yk[q] = cplx{em_modal(l, wk, w1, t1, nullptr), em_modal(l, wk, w2, t2, nullptr)};
+      }
+      ys[q * 128 + tid] = yk[q];
+    }
+    __syncthreads();
+    cplx v[P1];
+#pragma unroll
+    for (int q = 0; q < P1; ++q) {
+      v[q] = cplx{0.0, 0.0};
+      if (q < QMAX) {
+        const int k = j + q * P2;
+        if (active && k < N) {
+          const int kk = N - k;                      // mirror mode; kk == N (k == 0) has no partner
+          cplx ym = cplx{0.0, 0.0};
+          if (kk < N) ym = ys[(kk >> kLongLog2P2) * 128 + partner];
+          const cplx z = cplx{yk[q].x + ym.y, yk[q].y - ym.x};
+          v[q] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
+        }
+      }
+    }
+    __syncthreads();
+    if (active) {
+      DftAny<P1, -1>::run(v);
+      cplx* x = p.w.x + (long long)s * P;
+      x[j] = v[0];
+#pragma unroll
+      for (int r = 1; r < P1; ++r) x[(long long)r * P2 + j] = cmul(v[r], twt[r * 128 + tid]);
+    }
+  }
+}
+
 // Position (inside the P-point buffer) where the row DIT expects spectrum entry k: row k mod P1, digit-
 // reversed place of k / P1 inside the row.
 template <int LOG2P1> __device__ __forceinline__ long long long_pos(int k) {

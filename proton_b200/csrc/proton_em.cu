@@ -165,7 +165,8 @@ struct proton_em_ctx {
   int64_t launches = 0;
   // long-line path: column twiddles per P1 and the wave scratch (grown on demand, reused by every call)
   em::cplx* d_twl[em::kLongMaxP1 + 1] = {};   // column twiddles per P1
-  static constexpr int kLanes = 3;          // waves of long transforms run round-robin on these streams
+  static constexpr int kLanes = 8;          // up to 8 streams; `lanes` of them are used (PROTON_EM_LANES, default 3)
+  int lanes = 3;
   cudaStream_t lane[kLanes] = {};
   cudaEvent_t ev_fork = nullptr, ev_join[kLanes] = {};
   // host-buffer path (proton_em_analyze_host): cached device staging, a copy stream, per-buffer events
@@ -285,11 +286,13 @@ int fft_group(bool blue, int log2p) {
 constexpr size_t kLongRowSmem = (em::padded_len<em::kLongLog2P2>() + em::stage_tw_total(em::kLongLog2P2)) * sizeof(em::cplx);
 inline size_t long_col_smem(int p1) { return (size_t)p1 * em::kLongColsPerCta * sizeof(em::cplx); }
 constexpr int kLongColBlocks = em::kLongP2 / em::kLongColsPerCta;
+inline size_t long_pair_smem(int p1) { return ((size_t)p1 + (size_t)(p1 + 1) / 2 + 1) * 128 * sizeof(em::cplx); }
 
 int init_long_attrs() {
   CU_TRY(cudaFuncSetAttribute(em::em_long_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLongRowSmem));
 #define M(q)                                                                                                              \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));        \
+  CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_paired_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_pair_smem(q))); \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));  \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));
   FOR_EACH_P1(M)
@@ -327,7 +330,7 @@ int ensure_long(proton_em_ctx* ctx, int p1, int cap, long long n_tr_total) {
     CU_TRY(cudaGetLastError());
     CU_TRY(cudaStreamSynchronize(ctx->stream));     // the lanes read it without ordering against this stream
   }
-  const size_t lanes = proton_em_ctx::kLanes;
+  const size_t lanes = (size_t)ctx->lanes;
   const size_t need_x = lanes * (size_t)cap * (size_t)p1 * em::kLongP2;
   const size_t need_p = (size_t)std::max<long long>(n_tr_total, 1) * 2 * kLongColBlocks;
   if (ctx->long_x.n < need_x || ctx->long_part_v.n < need_p) {
@@ -342,6 +345,19 @@ int launch_long_colfwd(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::Co
   const dim3 grid(kLongColBlocks, groups);
   switch (p1) {
 #define M(q) case q: em::em_long_colfwd_kernel<q><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp); break;
+    FOR_EACH_P1(M)
+#undef M
+    default: return fail(PROTON_EM_EINVAL, "unsupported row count %d", p1);
+  }
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int launch_long_colfwd_paired(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::ColParams& cp, int groups) {
+  const dim3 grid(em::kLongPairBlocks, groups);
+  switch (p1) {
+#define M(q) case q: em::em_long_colfwd_paired_kernel<q><<<grid, 128, long_pair_smem(q), st>>>(cp); break;
     FOR_EACH_P1(M)
 #undef M
     default: return fail(PROTON_EM_EINVAL, "unsupported row count %d", p1);
@@ -558,6 +574,7 @@ int proton_em_create(proton_em_ctx** out, int device) {
     CU_TRY(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
   }
   CU_TRY(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+  if (const char* e = std::getenv("PROTON_EM_LANES")) ctx->lanes = std::max(1, std::min((int)proton_em_ctx::kLanes, std::atoi(e)));
   CU_TRY(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
   for (int i = 0; i < 2; ++i) {
     CU_TRY(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
@@ -889,8 +906,8 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
   CU_TRY(cudaMemcpyAsync(ctx->long_tr_pair.p, tr_pair.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
   // fork: the lanes start after everything queued so far on the main stream (uploads above included)
   CU_TRY(cudaEventRecord(ctx->ev_fork, ctx->stream));
-  for (int i = 0; i < proton_em_ctx::kLanes; ++i) CU_TRY(cudaStreamWaitEvent(ctx->lane[i], ctx->ev_fork, 0));
-  const size_t lane_stride = ctx->long_x.n / proton_em_ctx::kLanes;     // complex elements per lane
+  for (int i = 0; i < ctx->lanes; ++i) CU_TRY(cudaStreamWaitEvent(ctx->lane[i], ctx->ev_fork, 0));
+  const size_t lane_stride = ctx->long_x.n / (size_t)ctx->lanes;     // complex elements per lane
   int wave = 0;
   long long base = 0;
   for (const auto* cl : longs) {
@@ -902,7 +919,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
     for (int i = 0; i < cl->count; ++i) maxN = std::max(maxN, p->num_nodes[p->h_class_lines[cl->offset + i]]);
     for (long long s0 = 0; s0 < n_tr; s0 += cap, ++wave) {
       const int cnt = (int)std::min<long long>(cap, n_tr - s0);
-      const int li = wave % proton_em_ctx::kLanes;
+      const int li = wave % ctx->lanes;
       cudaStream_t st = ctx->lane[li];
       em::cplx* xbuf = ctx->long_x.p + (size_t)li * lane_stride;
       em::LongWave w{};
@@ -919,7 +936,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
       em::RowParams rp{xbuf, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
                        ctx->d_tw[em::kLongLog2P2]};
       int rc;
-      if (blue) rc = launch_long_colfwd(ctx, st, lp1, cp, groups);
+      if (blue) rc = launch_long_colfwd_paired(ctx, st, lp1, cp, groups);
       else rc = launch_long_scatter(ctx, st, lp1, w, maxN);
       if (rc) return rc;
       rc = launch_long_row(ctx, st, rp, cnt);
@@ -930,7 +947,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
     base += n_tr;
   }
   // join: later work on the main stream waits for every lane
-  for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
+  for (int i = 0; i < ctx->lanes; ++i) {
     CU_TRY(cudaEventRecord(ctx->ev_join[i], ctx->lane[i]));
     CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0));
   }
