@@ -250,6 +250,7 @@ struct SmallParams {
   int* amx;
   unsigned char* flag;
   double critical;
+  int max_nodes;               // longest line of the class (sizes the dense kernel's shared memory)
 };
 
 __global__ void __launch_bounds__(128) em_eval_small_kernel(const SmallParams p) {
@@ -405,6 +406,104 @@ __global__ void em_exp_probe_kernel(const double* x, double* y, long long n, con
 __global__ void em_expm1_probe_kernel(const double* x, double* y, long long n) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     y[i] = em_expm1_ref(x[i]);
+}
+
+}  // namespace em
+
+namespace em {
+
+// ---------------------------------------------------------------------------------------------
+// Short lines on the FP64 tensor-core path: sigma[N x T] = C[N x N] * Y[N x T] as DMMA m8n8k4 tiles
+// (C[n][k] = cos(pi k (2n+1) / 2N), Y[k][t] = modal value of mode k at timestamp t).  One CTA per (line, chunk of
+// timestamps): the cosine matrix is built once in shared memory in A-fragment order, every warp then takes tiles of 8
+// timestamps; each lane evaluates the modal factor of exactly the (k, t) element the B fragment wants from it, so no
+// data is exchanged between lanes before the MMAs.  Replaces calc_analytical_solution + idct1d
+// (bin/EMtool_analytical@0xc68c, @0xc2a0) for N <= kDenseMaxN.
+// ---------------------------------------------------------------------------------------------
+constexpr int kDenseMaxN = 96;
+
+__device__ __forceinline__ void dmma_m8n8k4(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+               : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+template <int MTMAX>    // m-tiles of 8 nodes the instantiation can hold: lines of up to 8 * MTMAX nodes
+__global__ void __launch_bounds__(128) em_eval_dense_kernel(const SmallParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* ctab = reinterpret_cast<double*>(smem_raw);              // [4 * Nmax]
+  double* afrag = ctab + 4 * p.max_nodes;                          // [MT * KS * 32]
+  const int item = blockIdx.x;
+  const int li = item / p.chunks, chunk = item - li * p.chunks;
+  const int line = p.class_lines[li];
+  const int N = p.num_nodes[line];
+  const double a = p.a_coeff[line];
+  const long long noff = p.node_off[line];
+  const int MT = (N + 7) >> 3, KS = (N + 3) >> 2;
+  for (int m = threadIdx.x; m < 4 * N; m += blockDim.x) ctab[m] = em_cos_frac((unsigned long long)m, 2ULL * N);
+  __syncthreads();
+  // A fragment of tile (mt, ks): lane holds C[n = 8 mt + lane/4][k = 4 ks + lane%4]
+  for (int e = threadIdx.x; e < MT * KS * 32; e += blockDim.x) {
+    const int l = e & 31, t = e >> 5;
+    const int ks = t % KS, mt = t / KS;
+    const int n = 8 * mt + (l >> 2), k = 4 * ks + (l & 3);
+    afrag[e] = (n < N && k < N) ? ctab[(k * (2 * n + 1)) % (4 * N)] : 0.0;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const double* lam = p.tabs[p.line_tab[line]].lam;
+  const double* W = p.W + noff;
+  const int j0 = chunk * p.ts_per_chunk, j1 = min(p.T, j0 + p.ts_per_chunk);
+  const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+  for (int tb = j0 + 8 * warp; tb < j1; tb += 8 * nwarps) {
+    const int tB = tb + (lane >> 2);                       // timestamp of this lane's B elements
+    const bool tvalid = tB < j1;
+    const double tt = p.ts[tvalid ? tB : j0];
+    const double w = __dmul_rn(a, tt);
+    double d[MTMAX][2];
+#pragma unroll
+    for (int mt = 0; mt < MTMAX; ++mt) { d[mt][0] = 0.0; d[mt][1] = 0.0; }
+    for (int ks = 0; ks < KS; ++ks) {
+      const int k = 4 * ks + (lane & 3);
+      double b = 0.0;
+      if (k < N && tvalid) {
+        double wk = W[k];
+        if (k > 0) wk = wk + wk;              // W carries Makhoul's 1/2 for k >= 1; the plain cosine sum does not want it
+        b = em_modal(lam[k], wk, w, tt, nullptr);
+      }
+      const double* af = afrag + ks * 32 + lane;
+#pragma unroll
+      for (int mt = 0; mt < MTMAX; ++mt)
+        if (mt < MT) dmma_m8n8k4(d[mt][0], d[mt][1], af[mt * KS * 32], b);
+    }
+    // D fragment: lane holds sigma[n = 8 mt + lane/4][t = tb + 2 (lane%4) + {0, 1}]
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int tj = tb + 2 * (lane & 3) + e;
+      double best = ninf;
+      int besti = 0x7fffffff;
+#pragma unroll
+      for (int mt = 0; mt < MTMAX; ++mt) {
+        const int n = 8 * mt + (lane >> 2);
+        if (mt < MT && n < N && tj < j1) {
+          const double v = d[mt][e];
+          if (p.stress) __stcs(p.stress + noff * (long long)p.T + (long long)tj * N + n, v);
+          if (v > best) { best = v; besti = n; }
+        }
+      }
+#pragma unroll
+      for (int o = 4; o < 32; o <<= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+        if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+      }
+      const double first = __shfl_sync(0xffffffffu, d[0][e], lane & 3);   // n = 0 lives in lanes 0..3 of tile 0
+      if ((lane >> 2) == 0 && tj < j1) {
+        if (besti == 0x7fffffff) { besti = 0; best = first; }
+        const long long o = (long long)line * p.T + tj;
+        p.mx[o] = best; p.amx[o] = besti; p.flag[o] = (best > p.critical) ? 1 : 0;
+      }
+    }
+  }
 }
 
 }  // namespace em

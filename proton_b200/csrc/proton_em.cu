@@ -81,8 +81,19 @@ enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_LPOW2 = 3, CLS_L
 // log2p = log2 of the FFT length for the in-CTA classes; for the long classes it holds P1 (rows of 4096 points).
 struct ClassOf { LineClass cls; int log2p; };
 
+// Lines up to this length take the dense (DMMA) path; the split against the FFT path is set from measured
+// throughput, PROTON_EM_DENSE_MAX overrides it for experiments (<= 64; the table kernel needs <= 32).
+int small_max_n() {
+  static const int v = [] {
+    const char* e = std::getenv("PROTON_EM_DENSE_MAX");
+    const int x = e ? std::atoi(e) : 0;
+    return x > 0 ? std::min(x, (int)em::kDenseMaxN) : 88;
+  }();
+  return v;
+}
+
 ClassOf classify(int N) {
-  if (N <= em::kSmallMaxN) return {CLS_SMALL, 0};
+  if (N <= small_max_n() && !(N >= 64 && (N & (N - 1)) == 0)) return {CLS_SMALL, 0};
   if ((N & (N - 1)) == 0) {
     if (N > kMaxLongPow2N) return {CLS_NONE, 0};
     if (N > kMaxPow2N) return {CLS_LPOW2, N / em::kLongP2};
@@ -619,6 +630,12 @@ int proton_em_create(proton_em_ctx** out, int device) {
   }
   int rc = init_kernel_attrs();
   if (rc == PROTON_EM_OK) rc = init_long_attrs();
+  if (rc == PROTON_EM_OK) {
+    const int n = em::kDenseMaxN;
+    const cudaError_t e = cudaFuncSetAttribute(em::em_eval_dense_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)((4 * n + (n / 8) * (n / 4) * 32) * sizeof(double)));
+    if (e != cudaSuccess) rc = fail(PROTON_EM_ECUDA, "cudaFuncSetAttribute(dense): %s", cudaGetErrorString(e));
+  }
   if (rc) { proton_em_destroy(ctx); return rc; }
   *out = ctx;
   return PROTON_EM_OK;
@@ -994,12 +1011,41 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
   for (int ci = chunk_begin; ci < chunk_end; ++ci)
   for (const auto& cl : p->chunks[ci].classes) {
     if (cl.cls == CLS_SMALL) {
+      // dense contraction on the FP64 tensor cores (DMMA); PROTON_EM_SMALL=table selects the cosine-table kernel
+      static const bool use_table = [] { const char* e = std::getenv("PROTON_EM_SMALL"); return e && std::strcmp(e, "table") == 0 && small_max_n() <= em::kSmallMaxN; }();
+      if (!use_table) {
+        // the class list is sorted longest first: cut it where the number of 8-node tiles drops to 8 and to 4
+        int begin = 0;
+        const int limits[3] = {64, 32, 0};
+        for (int part = 0; part < 3 && begin < cl.count; ++part) {
+          int end = begin;
+          while (end < cl.count && p->num_nodes[p->h_class_lines[cl.offset + end]] > limits[part]) ++end;
+          if (end == begin) continue;
+          const int cnt = end - begin;
+          const int maxN = p->num_nodes[p->h_class_lines[cl.offset + begin]];
+          int chunks = (int)std::min<long long>((T + 31) / 32, std::max<long long>(1, target_items / cnt));
+          int tpc = (((T + chunks - 1) / chunks) + 7) / 8 * 8;
+          chunks = (T + tpc - 1) / tpc;
+          em::SmallParams sp{p->d_class_lines.p + cl.offset + begin, cnt, chunks, tpc, T, p->d_num_nodes, p->d_a,
+                             p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_exp,
+                             d_stress, d_mx, d_amx, d_flag, critical, maxN};
+          const size_t smem = (size_t)(4 * maxN + ((maxN + 7) / 8) * ((maxN + 3) / 4) * 32) * sizeof(double);
+          const unsigned items = (unsigned)((long long)cnt * chunks);
+          if (maxN > 64) em::em_eval_dense_kernel<12><<<items, 128, smem, ctx->stream>>>(sp);
+          else if (maxN > 32) em::em_eval_dense_kernel<8><<<items, 128, smem, ctx->stream>>>(sp);
+          else em::em_eval_dense_kernel<4><<<items, 128, smem, ctx->stream>>>(sp);
+          ctx->launches++;
+          CU_TRY(cudaGetLastError());
+          begin = end;
+        }
+        continue;
+      }
       int chunks = (int)std::min<long long>(T, std::max<long long>(1, target_items * 4 / cl.count));
       int tpc = (T + chunks - 1) / chunks;
       chunks = (T + tpc - 1) / tpc;
       em::SmallParams sp{p->d_class_lines.p + cl.offset, cl.count, chunks, tpc, T, p->d_num_nodes, p->d_a,
                          p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_exp,
-                         d_stress, d_mx, d_amx, d_flag, critical};
+                         d_stress, d_mx, d_amx, d_flag, critical, 0};
       const long long items = (long long)cl.count * chunks;
       em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, ctx->stream>>>(sp);
       ctx->launches++;
