@@ -1,61 +1,75 @@
-"""`Analytical_Class`: the in-process twin of the reference launcher class of the same name
-(analytical_class_cli.py:6-91).  Same constructor arguments, same `analytical_function()` contract: it reads the
-`analytical.txt` the formulation wrote, writes `analytical.cfg` with the four keys the kernel reads, runs the kernel —
-here `proton_em_run_cfg` inside this process instead of `os.system(bin/EMtool_analytical ...)` — and returns the same
-message texts (callers only test for the substring "seconds", PROTON_cli.py:680)."""
+"""In-process stand-in for PROTON's kernel launcher class.
+
+PROTON's GUI and CLI construct `Analytical_Class(sim_time, directory, selected_line, TECHNOLOGY, TEMPERATURE, WIDTH,
+IS_LINUX, INSTALLATION_FOLDER)` and call `analytical_function()`, which turns the formulation's `analytical.txt` into an
+`analytical.cfg`, starts `bin/EMtool_analytical` as a child process and maps its exit status to a message
+(analytical_class_cli.py:6-91).  Callers only look for the word "seconds" in the returned text (PROTON_cli.py:680,
+GUI_auxiliary.py:1438).  This class keeps that surface but runs the kernel through `proton_em_run_cfg` in the calling
+process: no shell, no `. /opt/intel/oneapi/.../vars.sh` prefix (which aborts dash on boxes without oneAPI),
+one CUDA context for any number of lines.
+"""
 from __future__ import annotations
 
-import os
+import re
 import time
+from pathlib import Path
+from typing import Optional, Tuple
 
 from .api import Context
 
+_KEYVAL = re.compile(r"^\s*(nx_total|Acoef)\s*=\s*(\S+)", re.MULTILINE)
 
-class Analytical_Class():
 
-  def __init__(self, sim_time, directory, selected_line, TECHNOLOGY, TEMPERATURE, WIDTH, IS_LINUX=True,
-               INSTALLATION_FOLDER="", ctx=None):
-    self.sim_time = sim_time
-    self.directory = directory
-    self.selected_line = selected_line
-    self.TECHNOLOGY = TECHNOLOGY
-    self.TEMPERATURE = TEMPERATURE
-    self.WIDTH = WIDTH
-    self.IS_LINUX = IS_LINUX
-    self.INSTALLATION_FOLDER = INSTALLATION_FOLDER
-    self._ctx = ctx
+def _read_formulation_summary(path: Path) -> Tuple[str, str]:
+    """(`nx_total`, `Acoef`) as the strings `matrix_formulation` wrote (matrix_formulation_func_cli.py:283-286)."""
+    found = dict(_KEYVAL.findall(path.read_text()))
+    return found.get("nx_total", ""), found.get("Acoef", "")
 
-  def analytical_function(self):
-    Acoef = ""
-    nxTotal = ""
-    if not self.selected_line:
-      return('No line was selected and discretized prior to simulation.')
-    line_path = self.selected_line+"/"+self.TECHNOLOGY+"_"+str(self.TEMPERATURE)+"_"+str(self.WIDTH)+"/"
-    analytical_file = self.directory+"/"+"input"+"/"+line_path+"analytical.txt"
-    try:
-      with open(analytical_file) as f_anal:
-        for line in f_anal.readlines():
-          words = line.split()
-          if 'Acoef' in words: Acoef = words[2]
-          if 'nx_total' in words: nxTotal = words[2]
-    except FileNotFoundError:
-      return(f"No discretization has been performed for line {self.selected_line} with params: {self.TECHNOLOGY}, {self.TEMPERATURE}, {self.WIDTH}.")
-    input_files = self.directory + "/input/"+line_path
-    if not os.path.exists(input_files):
-      return(f'Input files directory for {self.selected_line} does not exist.')
-    config_file = self.directory+"/input/"+line_path+"analytical.cfg"
-    with open(config_file, "w") as f:
-      f.write(f"input_files {input_files}\nnum_nodes {nxTotal}\n")
-      f.write(f"A_coeff {Acoef}\nsimulation_time {self.sim_time}\n")
-    start_time = time.time()
-    own = self._ctx is None
-    ctx = self._ctx or Context(0)
-    try:
-      return_value, text = ctx.run_cfg(config_file)
-    finally:
-      if own:
-        ctx.close()
-    elapsed_time = time.time() - start_time
-    if return_value == 0:
-      return(f"EM stress analysis was successfully performed in {elapsed_time:.3f} seconds for the line {self.selected_line} (Configuration: {self.TECHNOLOGY}, {self.TEMPERATURE}K, {self.WIDTH}um).")
-    return(f"Line analysis terminated with unknown error {return_value}. {text.strip()}")
+
+class Analytical_Class:
+    def __init__(self, sim_time, directory, selected_line, TECHNOLOGY, TEMPERATURE, WIDTH, IS_LINUX=True,
+                 INSTALLATION_FOLDER="", ctx: Optional[Context] = None):
+        self.sim_time, self.directory, self.selected_line = sim_time, directory, selected_line
+        self.TECHNOLOGY, self.TEMPERATURE, self.WIDTH = TECHNOLOGY, TEMPERATURE, WIDTH
+        self.IS_LINUX, self.INSTALLATION_FOLDER = IS_LINUX, INSTALLATION_FOLDER
+        self._ctx = ctx
+
+    # -- helpers ---------------------------------------------------------------------------------------------
+    def _config_tag(self) -> str:
+        return f"{self.TECHNOLOGY}_{self.TEMPERATURE}_{self.WIDTH}"
+
+    def _input_dir(self) -> Path:
+        return Path(self.directory) / "input" / str(self.selected_line) / self._config_tag()
+
+    def _write_cfg(self, nodes: str, acoef: str) -> Path:
+        folder = f"{self.directory}/input/{self.selected_line}/{self._config_tag()}/"
+        cfg = Path(folder) / "analytical.cfg"
+        cfg.write_text("".join(f"{k} {v}\n" for k, v in (("input_files", folder), ("num_nodes", nodes),
+                                                          ("A_coeff", acoef), ("simulation_time", self.sim_time))))
+        return cfg
+
+    # -- the reference's entry point ---------------------------------------------------------------------------
+    def analytical_function(self) -> str:
+        if not self.selected_line:
+            return "No line was selected and discretized prior to simulation."
+        folder = self._input_dir()
+        try:
+            nodes, acoef = _read_formulation_summary(folder / "analytical.txt")
+        except FileNotFoundError:
+            return (f"No discretization has been performed for line {self.selected_line} with params: "
+                    f"{self.TECHNOLOGY}, {self.TEMPERATURE}, {self.WIDTH}.")
+        if not folder.is_dir():
+            return f"Input files directory for {self.selected_line} does not exist."
+        cfg = self._write_cfg(nodes, acoef)
+        started = time.time()
+        ctx = self._ctx if self._ctx is not None else Context(0)
+        try:
+            status, kernel_text = ctx.run_cfg(str(cfg))
+        finally:
+            if self._ctx is None:
+                ctx.close()
+        took = time.time() - started
+        if status == 0:
+            return (f"EM stress analysis was successfully performed in {took:.3f} seconds for the line "
+                    f"{self.selected_line} (Configuration: {self.TECHNOLOGY}, {self.TEMPERATURE}K, {self.WIDTH}um).")
+        return f"Line analysis terminated with unknown error {status}. {kernel_text.strip()}"
