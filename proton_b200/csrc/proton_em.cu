@@ -892,7 +892,7 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
 // round-robin to the lanes (streams) so that small waves of different classes overlap; one join, one reduction.
 static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_plan::ClassList*>& longs,
                          const double* d_ts, int T, double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag,
-                         double critical) {
+                         double critical, long long* n_tr_out) {
   proton_em_ctx* ctx = p->ctx;
   const int npairs = (T + 1) / 2;
   long long n_tr_total = 0;
@@ -963,21 +963,27 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
     }
     base += n_tr;
   }
-  // join: later work on the main stream waits for every lane
+  *n_tr_out = n_tr_total;
+  return PROTON_EM_OK;
+}
+
+// Join of the lanes and the one reduction of the column-block partials (queued after the other classes so that
+// their kernels overlap the long waves).
+static int eval_long_finish(proton_em_plan* p, long long n_tr_total, int T, double* d_stress, double* d_mx, int* d_amx,
+                            unsigned char* d_flag, double critical) {
+  proton_em_ctx* ctx = p->ctx;
   for (int i = 0; i < ctx->lanes; ++i) {
     CU_TRY(cudaEventRecord(ctx->ev_join[i], ctx->lane[i]));
     CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0));
   }
-  {   // one reduction of the column-block partials for all long transforms of the chunk
-    em::LongWave w{};
-    w.tr_line = ctx->long_tr_line.p; w.tr_pair = ctx->long_tr_pair.p; w.n_tr = (int)n_tr_total; w.T = T;
-    w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
-    w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
-    w.critical = critical;
-    em::em_long_reduce_kernel<<<(unsigned)((2 * n_tr_total + 127) / 128), 128, 0, ctx->stream>>>(w, kLongColBlocks);
-    ctx->launches++;
-    CU_TRY(cudaGetLastError());
-  }
+  em::LongWave w{};
+  w.tr_line = ctx->long_tr_line.p; w.tr_pair = ctx->long_tr_pair.p; w.n_tr = (int)n_tr_total; w.T = T;
+  w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
+  w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
+  w.critical = critical;
+  em::em_long_reduce_kernel<<<(unsigned)((2 * n_tr_total + 127) / 128), 128, 0, ctx->stream>>>(w, kLongColBlocks);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
   return PROTON_EM_OK;
 }
 
@@ -1004,8 +1010,9 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
     for (const auto& cl : p->chunks[ci].classes)
       if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) longs.push_back(&cl);
   // long lines first: their waves run on the lanes while the main stream works through the other classes
+  long long n_long_tr = 0;
   if (!longs.empty()) {
-    int rc = eval_long_all(p, longs, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical);
+    int rc = eval_long_all(p, longs, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical, &n_long_tr);
     if (rc) return rc;
   }
   for (int ci = chunk_begin; ci < chunk_end; ++ci)
@@ -1069,6 +1076,7 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
     int rc = launch_eval_fft(ctx, blue, cl.log2p, ep, (int)grid);
     if (rc) return rc;
   }
+  if (n_long_tr > 0) return eval_long_finish(p, n_long_tr, T, d_stress, d_mx, d_amx, d_flag, critical);
   return PROTON_EM_OK;
 }
 
