@@ -265,12 +265,12 @@ int launch_tables(proton_em_ctx* ctx, int log2p, const em::NTab* d_entries, int 
   return PROTON_EM_OK;
 }
 
-int launch_eval_fft(proton_em_ctx* ctx, bool blue, int log2p, const em::EvalParams& ep, int grid) {
+int launch_eval_fft(proton_em_ctx* ctx, cudaStream_t st, bool blue, int log2p, const em::EvalParams& ep, int grid) {
   switch (log2p) {
 #define M(p)                                                                                                       \
   case p:                                                                                                          \
-    if (blue) em::em_eval_fft_kernel<p, true><<<grid, em::Cfg<p, true>::NT, em::Cfg<p, true>::smem_bytes, ctx->stream>>>(ep); \
-    else em::em_eval_fft_kernel<p, false><<<grid, em::Cfg<p, false>::NT, em::Cfg<p, false>::smem_bytes, ctx->stream>>>(ep);  \
+    if (blue) em::em_eval_fft_kernel<p, true><<<grid, em::Cfg<p, true>::NT, em::Cfg<p, true>::smem_bytes, st>>>(ep); \
+    else em::em_eval_fft_kernel<p, false><<<grid, em::Cfg<p, false>::NT, em::Cfg<p, false>::smem_bytes, st>>>(ep);  \
     break;
     FOR_EACH_LOG2P(M)
 #undef M
@@ -976,6 +976,7 @@ static int eval_long_finish(proton_em_plan* p, long long n_tr_total, int T, doub
     CU_TRY(cudaEventRecord(ctx->ev_join[i], ctx->lane[i]));
     CU_TRY(cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0));
   }
+  if (n_tr_total <= 0) return PROTON_EM_OK;
   em::LongWave w{};
   w.tr_line = ctx->long_tr_line.p; w.tr_pair = ctx->long_tr_pair.p; w.n_tr = (int)n_tr_total; w.T = T;
   w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
@@ -1009,14 +1010,21 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
   for (int ci = chunk_begin; ci < chunk_end; ++ci)
     for (const auto& cl : p->chunks[ci].classes)
       if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) longs.push_back(&cl);
-  // long lines first: their waves run on the lanes while the main stream works through the other classes
+  // Every class kernel goes to one of the lanes (streams forked off the main stream) so that the tails of the
+  // per-class launches overlap; the long lines' waves use the same lanes.  One join at the end.
   long long n_long_tr = 0;
-  if (!longs.empty()) {
+  int next_lane = 0;
+  if (longs.empty()) {
+    CU_TRY(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    for (int i = 0; i < ctx->lanes; ++i) CU_TRY(cudaStreamWaitEvent(ctx->lane[i], ctx->ev_fork, 0));
+  } else {
     int rc = eval_long_all(p, longs, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical, &n_long_tr);
     if (rc) return rc;
   }
   for (int ci = chunk_begin; ci < chunk_end; ++ci)
   for (const auto& cl : p->chunks[ci].classes) {
+    if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) continue;
+    cudaStream_t cst = ctx->lane[next_lane++ % ctx->lanes];
     if (cl.cls == CLS_SMALL) {
       // dense contraction on the FP64 tensor cores (DMMA); PROTON_EM_SMALL=table selects the cosine-table kernel
       static const bool use_table = [] { const char* e = std::getenv("PROTON_EM_SMALL"); return e && std::strcmp(e, "table") == 0 && small_max_n() <= em::kSmallMaxN; }();
@@ -1038,9 +1046,9 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
                              d_stress, d_mx, d_amx, d_flag, critical, maxN};
           const size_t smem = (size_t)(4 * maxN + ((maxN + 7) / 8) * ((maxN + 3) / 4) * 32) * sizeof(double);
           const unsigned items = (unsigned)((long long)cnt * chunks);
-          if (maxN > 64) em::em_eval_dense_kernel<12><<<items, 128, smem, ctx->stream>>>(sp);
-          else if (maxN > 32) em::em_eval_dense_kernel<8><<<items, 128, smem, ctx->stream>>>(sp);
-          else em::em_eval_dense_kernel<4><<<items, 128, smem, ctx->stream>>>(sp);
+          if (maxN > 64) em::em_eval_dense_kernel<12><<<items, 128, smem, cst>>>(sp);
+          else if (maxN > 32) em::em_eval_dense_kernel<8><<<items, 128, smem, cst>>>(sp);
+          else em::em_eval_dense_kernel<4><<<items, 128, smem, cst>>>(sp);
           ctx->launches++;
           CU_TRY(cudaGetLastError());
           begin = end;
@@ -1054,12 +1062,11 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
                          p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_exp,
                          d_stress, d_mx, d_amx, d_flag, critical, 0};
       const long long items = (long long)cl.count * chunks;
-      em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, ctx->stream>>>(sp);
+      em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, cst>>>(sp);
       ctx->launches++;
       CU_TRY(cudaGetLastError());
       continue;
     }
-    if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) continue;
     const bool blue = cl.cls == CLS_BLUE;
     const int G = fft_group(blue, cl.log2p);
     const int npairs = (T + 1) / 2;
@@ -1073,11 +1080,10 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
                       ctx->d_pos[cl.log2p], d_stress, d_mx, d_amx, d_flag, critical};
     const long long grid = (long long)cl.count * chunks;
     if (grid > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many work items");
-    int rc = launch_eval_fft(ctx, blue, cl.log2p, ep, (int)grid);
+    int rc = launch_eval_fft(ctx, cst, blue, cl.log2p, ep, (int)grid);
     if (rc) return rc;
   }
-  if (n_long_tr > 0) return eval_long_finish(p, n_long_tr, T, d_stress, d_mx, d_amx, d_flag, critical);
-  return PROTON_EM_OK;
+  return eval_long_finish(p, n_long_tr, T, d_stress, d_mx, d_amx, d_flag, critical);
 }
 
 int proton_em_eval(proton_em_plan* p, const double* ts, int32_t T, const proton_em_opts* opts,
