@@ -296,12 +296,22 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
   }
 }
 
+// The two innermost stages (strides R and 1) of a plan that ends in two equal radices touch, per thread, the same
+// blocks of R*R consecutive points, and both give butterfly b of transform g to the same thread: a warp's outputs of
+// one are exactly its inputs of the other, so a warp barrier replaces the CTA barrier between them.
+template <int LOG2P, int I> __host__ __device__ constexpr bool warp_local_after() {   // between stage I and stage I+1
+  return I + 1 == plan_n(LOG2P) - 1 && plan_radix(LOG2P, I) == plan_radix(LOG2P, I + 1);
+}
+template <int LOG2P, int I> __device__ __forceinline__ void stage_barrier() {
+  if constexpr (warp_local_after<LOG2P, I>()) __syncwarp(); else __syncthreads();
+}
+
 // Stage recursion helpers (compile-time unrolled over the plan).
 template <int LOG2P, int I, int IEND, int NT> struct DifStages {   // stages I .. IEND-1, SIGN = -1
   static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
     if constexpr (I < IEND) {
       fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), true, -1, NT, stage_tw_offset(LOG2P, I)>(data, gcount, tw, tid);
-      __syncthreads();
+      stage_barrier<LOG2P, I>();
       DifStages<LOG2P, I + 1, IEND, NT>::run(data, gcount, tw, tid);
     }
   }
@@ -310,7 +320,7 @@ template <int LOG2P, int I, int ISTOP, int NT> struct DitStages {   // stages I 
   static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
     if constexpr (I >= ISTOP) {
       fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), false, +1, NT, stage_tw_offset(LOG2P, I)>(data, gcount, tw, tid);
-      __syncthreads();
+      if constexpr (I >= 1) stage_barrier<LOG2P, I - 1>(); else __syncthreads();
       DitStages<LOG2P, I - 1, ISTOP, NT>::run(data, gcount, tw, tid);
     }
   }
@@ -403,7 +413,7 @@ em_eval_fft_kernel(const EvalParams prm) {
       __syncthreads();
       DifStages<LOG2P, 1, NST - 1, NT>::run(data, gcount, twb, tid);
       fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, gcount, tab.hhat, tid);
-      __syncthreads();
+      stage_barrier<LOG2P, NST - 2>();
       DitStages<LOG2P, NST - 2, 1, NT>::run(data, gcount, twb, tid);
     } else {
       DitStages<LOG2P, NST - 1, 1, NT>::run(data, gcount, twb, tid);

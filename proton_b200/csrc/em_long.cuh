@@ -406,7 +406,7 @@ __global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_lo
     }
     const cplx* hh = p.tabs[p.line_tab[p.tr_line[s]]].hhat + (long long)r * P2;
     fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, 1, hh, tid);
-    __syncthreads();
+    stage_barrier<LOG2P, NST - 2>();
     DitStages<LOG2P, NST - 2, 0, NT>::run(data, 1, twb, tid);
   } else {
     DitStages<LOG2P, NST - 1, 0, NT>::run(data, 1, twb, tid);
