@@ -242,6 +242,7 @@ def main():
     import torch
     import torch.distributed as dist
     from proton_b200.api import Context, EvalResult
+    from proton_b200 import workloads as W
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)
@@ -328,16 +329,61 @@ def main():
         evals_total = float(evals_rank)
     value = evals_total / (ms * 1e-3)
 
-    # ---- roofline of the evaluation step (rank 0's share) -------------------------------------------------
+    # ---- roofline (rank 0's share) ---------------------------------------------------------------------------
     # algorithmic bytes per eval: 8 B stress write + the per-line inputs read once per step (16 B per mode:
-    # lambda_k and W_k) + 13 B of reductions per (line, t)  ->  8 + 16/T + 13/N  (DESIGN.md §5)
+    # lambda_k and W_k) + 13 B of reductions per (line, t)  ->  8 + 16/T + 13/N  (SURVEY.md §8d, DESIGN.md §5)
     peak, peak_src = measured_peaks()
     alg_bytes = evals_rank * 8.0 + batch.total_nodes * 16.0 + L * T * 13.0
     t_rank = ms * 1e-3
-    achieved = alg_bytes / t_rank / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src,
-                "note": "whole evaluation step (all length classes); FP64-pipe bound kernels, see DESIGN.md §5"}
+    step_gbs = alg_bytes / t_rank / 1e9
+    # Per-kernel live timing: the same step again with a CUDA event pair around every launch, on the stream it is
+    # launched on (proton_em_profile).  Kernels of different lanes overlap, so the per-kernel sums exceed the step.
+    nn = batch.num_nodes.astype(np.int64)
+    kinds = np.array([W.kernel_class(int(n)) for n in nn])
+    evals_by_kind = {k: float(nn[kinds == k].sum()) * T for k in set(kinds.tolist())}
+    long_evals = evals_by_kind.get("long_blue", 0.0) + evals_by_kind.get("long_pow2", 0.0)
+    evals_through = {"em_eval_dense_kernel": evals_by_kind.get("dense", 0.0), "em_eval_small_kernel": 0.0,
+                     "em_eval_fft_kernel<pow2>": evals_by_kind.get("fft_pow2", 0.0),
+                     "em_eval_fft_kernel<bluestein>": evals_by_kind.get("fft_blue", 0.0),
+                     "em_long_colfwd_paired_kernel": evals_by_kind.get("long_blue", 0.0),
+                     "em_long_row_kernel": long_evals, "em_long_colinv_kernel": long_evals,
+                     "em_long_scatter_kernel": evals_by_kind.get("long_pow2", 0.0), "em_long_reduce_kernel": long_evals}
+    n_prof = max(1, min(args.steps, 5))
+    barrier()
+    ctx.profile(True)
+    for _ in range(n_prof):
+        plan.eval_device(d_ts, d_stress, d_mx, d_amx, d_flag, critical=CRITICAL)
+    ctx.profile(False)
+    prof = {k: v for k, v in ctx.profile_read().items() if v[1] > 0}
+    tot_ms = sum(v[0] for v in prof.values()) or 1.0
+    kernels = {k: {"ms_per_step": v[0] / n_prof, "launches_per_step": v[1] / n_prof, "avg_launch_us": 1e3 * v[0] / v[1],
+                   "share_of_kernel_time": v[0] / tot_ms} for k, v in prof.items()}
+    dom = max(prof, key=lambda k: prof[k][0])
+    dom_ms, dom_n = prof[dom][0] / n_prof, prof[dom][1] / n_prof
+    dom_bytes = 8.0 * evals_through.get(dom, 0.0)            # per step: 8 B per eval that passes through the kernel
+    achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+    traffic = None
+    tp = REPO / "profiles" / "r01_kernel_traffic.json"
+    if tp.exists():
+        traffic = json.loads(tp.read_text()).get(dom, {}).get("dram_bytes_per_launch")
+    # FP64 side: algorithmic flops = sum T N (2.5 log2 N + 5 + 22) against the measured DFMA peak
+    flops = float((nn * (2.5 * np.log2(np.maximum(nn, 2)) + 27.0)).sum()) * T
+    fp64_peak = 35.9
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": dom_bytes / dom_n, "avg_launch_us": 1e3 * dom_ms / dom_n,
+                "launches_per_step": dom_n, "share_of_kernel_time": kernels[dom]["share_of_kernel_time"],
+                "step": {"achieved": step_gbs, "frac": step_gbs / peak, "unit": "GB/s",
+                         "note": "all launches of one step, 8 + 16/T + 13/N bytes per eval over the step time"},
+                "fp64": {"achieved": flops / t_rank / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+                         "frac": flops / t_rank / 1e12 / fp64_peak,
+                         "note": "algorithmic flops T*N*(2.5 log2 N + 27) over the step time against the measured DFMA "
+                                 "peak (profiles/r01_fp64_peak.json); the kernels are FP64-pipe / shared-memory bound, "
+                                 "not HBM bound (DESIGN.md §5)"},
+                "kernels": kernels,
+                "note": "dominant kernel by summed live duration; achieved = 8 B x evals passing through it per step / its "
+                        "summed launch durations (CUDA events on the launching stream, kernels of other lanes running "
+                        "concurrently)"}
 
     # ---- e2e: public host-buffer call, pinned host memory, copies inside the timed region -----------------
     e2e = None

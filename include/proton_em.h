@@ -105,6 +105,13 @@ int proton_em_synchronize(proton_em_ctx* ctx);
 void* proton_em_stream(proton_em_ctx* ctx);
 /* Number of kernel launches issued by this ctx so far (bench.py reports it as gpu_launches). */
 int64_t proton_em_launch_count(const proton_em_ctx* ctx);
+/* Per-kernel timing for bench.py's roofline (no counterpart in the reference).  While enabled, every launch of
+ * the evaluation path is bracketed by a CUDA event pair on the stream it is launched on; the call synchronises
+ * the device, folds the finished pairs into per-kind totals, and (enable != 0 after being off) clears them.
+ * proton_em_profile_read returns name / total milliseconds / launch count of kernel kind 0, 1, ... and
+ * PROTON_EM_EINVAL past the last kind. */
+int proton_em_profile(proton_em_ctx* ctx, int enable);
+int proton_em_profile_read(const proton_em_ctx* ctx, int kind, const char** name, double* total_ms, int64_t* launches);
 
 /* One call for host callers: pack + eval + copy back, splitting the batch so that the device-side
  * stress buffer stays below max_device_bytes (0 = default).  This is the end-to-end path bench.py

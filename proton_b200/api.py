@@ -133,6 +133,20 @@ class Context:
     def launch_count(self) -> int:
         return int(self._lib.proton_em_launch_count(self._h))
 
+    def profile(self, enable: bool) -> None:
+        """Start (clears the totals) or stop the per-kernel CUDA-event timing of the evaluation path."""
+        check(self._lib.proton_em_profile(self._h, 1 if enable else 0))
+
+    def profile_read(self) -> dict:
+        """{kernel name: (total ms, launches)} accumulated since profile(True)."""
+        out, kind = {}, 0
+        while True:
+            name, ms, n = ctypes.c_char_p(), ctypes.c_double(), ctypes.c_int64()
+            if self._lib.proton_em_profile_read(self._h, kind, ctypes.byref(name), ctypes.byref(ms), ctypes.byref(n)) != 0:
+                return out
+            out[name.value.decode()] = (ms.value, int(n.value))
+            kind += 1
+
     @property
     def stream(self) -> int:
         return int(self._lib.proton_em_stream(self._h) or 0)

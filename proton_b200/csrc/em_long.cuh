@@ -383,6 +383,49 @@ struct RowParams {
   const cplx* tw;          // per-stage twiddle tables of the 4096-point transform
 };
 
+// Outermost stage (stride P2/8) of the row transform with one side in global memory: the DIF form reads its
+// butterfly inputs straight from the row (lanes read consecutive columns, so every access is a coalesced 512-byte
+// segment), the DIT form writes its outputs straight back.  Saves the staging pass through shared memory and one
+// CTA barrier at each end of the kernel.
+template <int NT>
+__device__ __forceinline__ void row_dif_from_global(const cplx* __restrict__ row, cplx* __restrict__ data,
+                                                    const cplx* __restrict__ twb, int tid) {
+  constexpr int LOG2P = kLongLog2P2, LOG2S = LOG2P - 3, S = 1 << LOG2S;
+  static_assert(plan_radix(LOG2P, 0) == 8, "outermost stage is radix 8");
+  for (int j = tid; j < S; j += NT) {
+    cplx v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = row[j + q * S];
+    Dft<8, -1>::run(v);
+    cplx w[8];
+    const cplx tv = twb[j];
+    tw_powers<8>(cplx{tv.x, -tv.y}, w);
+#pragma unroll
+    for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
+    cplx* d = data + pad_idx<LOG2P>(j);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) d[pad_off<LOG2P, LOG2S>(q)] = v[q];
+  }
+}
+template <int NT>
+__device__ __forceinline__ void row_dit_to_global(cplx* __restrict__ row, const cplx* __restrict__ data,
+                                                  const cplx* __restrict__ twb, int tid) {
+  constexpr int LOG2P = kLongLog2P2, LOG2S = LOG2P - 3, S = 1 << LOG2S;
+  for (int j = tid; j < S; j += NT) {
+    const cplx* d = data + pad_idx<LOG2P>(j);
+    cplx v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = d[pad_off<LOG2P, LOG2S>(q)];
+    cplx w[8];
+    tw_powers<8>(twb[j], w);
+#pragma unroll
+    for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
+    Dft<8, +1>::run(v);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) row[j + q * S] = v[q];
+  }
+}
+
 __global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_long_row_kernel(const RowParams p) {
   constexpr int LOG2P = kLongLog2P2, P2 = kLongP2, NT = kLongRowThreads, NST = plan_n(LOG2P);
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -393,10 +436,11 @@ __global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_lo
   for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = p.tw[i];
   const long long P = (long long)P2 * p.p1;
   cplx* row = p.x + (long long)s * P + (long long)r * P2;
-  for (int i = tid; i < P2; i += NT) data[pad_idx<LOG2P>(i)] = row[i];
-  __syncthreads();
   if (p.mode != 2) {
-    DifStages<LOG2P, 0, NST - 1, NT>::run(data, 1, twb, tid);
+    __syncthreads();                                  // twiddles in place
+    row_dif_from_global<NT>(row, data, twb, tid);
+    __syncthreads();
+    DifStages<LOG2P, 1, NST - 1, NT>::run(data, 1, twb, tid);
     if (p.mode == 1) {
       fft_stage<LOG2P, stage_radix<LOG2P, NST - 1>(), 0, true, -1, NT, 0>(data, 1, twb, tid);
       __syncthreads();
@@ -407,11 +451,13 @@ __global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_lo
     const cplx* hh = p.tabs[p.line_tab[p.tr_line[s]]].hhat + (long long)r * P2;
     fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, 1, hh, tid);
     stage_barrier<LOG2P, NST - 2>();
-    DitStages<LOG2P, NST - 2, 0, NT>::run(data, 1, twb, tid);
+    DitStages<LOG2P, NST - 2, 1, NT>::run(data, 1, twb, tid);
   } else {
-    DitStages<LOG2P, NST - 1, 0, NT>::run(data, 1, twb, tid);
+    for (int i = tid; i < P2; i += NT) data[pad_idx<LOG2P>(i)] = row[i];
+    __syncthreads();
+    DitStages<LOG2P, NST - 1, 1, NT>::run(data, 1, twb, tid);
   }
-  for (int i = tid; i < P2; i += NT) row[i] = data[pad_idx<LOG2P>(i)];
+  row_dit_to_global<NT>(row, data, twb, tid);
 }
 
 // ---- inverse column pass + epilogue -----------------------------------------------------------------------

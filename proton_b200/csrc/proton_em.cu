@@ -189,7 +189,42 @@ struct proton_em_ctx {
   DevBuf<em::cplx> long_x, long_y;
   DevBuf<double> long_part_v;
   DevBuf<int> long_part_i, long_tr_line, long_tr_pair;
+  // per-kernel timing (proton_em_profile): an event pair around every launch of the evaluation path
+  bool prof_on = false;
+  struct ProfRec { int kind; cudaEvent_t a, b; };
+  std::vector<ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
+  double prof_ms[16] = {};
+  long long prof_n[16] = {};
 };
+
+namespace {
+enum ProfKind { PK_DENSE = 0, PK_TABLE, PK_FFT_POW2, PK_FFT_BLUE, PK_LONG_COLFWD, PK_LONG_ROW, PK_LONG_COLINV,
+                PK_LONG_SCATTER, PK_LONG_REDUCE, PK_COUNT };
+const char* const kProfNames[PK_COUNT] = {"em_eval_dense_kernel", "em_eval_small_kernel", "em_eval_fft_kernel<pow2>",
+                                          "em_eval_fft_kernel<bluestein>", "em_long_colfwd_paired_kernel",
+                                          "em_long_row_kernel", "em_long_colinv_kernel", "em_long_scatter_kernel",
+                                          "em_long_reduce_kernel"};
+// Records an event before and after one launch on the stream it is launched on (only while profiling is on).
+struct ProfScope {
+  proton_em_ctx* ctx;
+  cudaStream_t st;
+  cudaEvent_t b = nullptr;
+  ProfScope(proton_em_ctx* c, int kind, cudaStream_t s) : ctx(c), st(s) {
+    if (!c->prof_on) return;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    for (cudaEvent_t& e : ev) {
+      if (!c->prof_pool.empty()) { e = c->prof_pool.back(); c->prof_pool.pop_back(); }
+      else if (cudaEventCreate(&e) != cudaSuccess) { e = nullptr; }
+    }
+    if (!ev[0] || !ev[1]) return;
+    cudaEventRecord(ev[0], s);
+    b = ev[1];
+    c->prof_recs.push_back({kind, ev[0], ev[1]});
+  }
+  ~ProfScope() { if (b) cudaEventRecord(b, st); }
+};
+}  // namespace
 
 struct proton_em_plan {
   proton_em_ctx* ctx = nullptr;
@@ -266,6 +301,7 @@ int launch_tables(proton_em_ctx* ctx, int log2p, const em::NTab* d_entries, int 
 }
 
 int launch_eval_fft(proton_em_ctx* ctx, cudaStream_t st, bool blue, int log2p, const em::EvalParams& ep, int grid) {
+  ProfScope prof(ctx, blue ? PK_FFT_BLUE : PK_FFT_POW2, st);
   switch (log2p) {
 #define M(p)                                                                                                       \
   case p:                                                                                                          \
@@ -367,6 +403,7 @@ int launch_long_colfwd(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::Co
 
 int launch_long_colfwd_paired(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::ColParams& cp, int groups) {
   const dim3 grid(em::kLongPairBlocks, groups);
+  ProfScope prof(ctx, PK_LONG_COLFWD, st);
   switch (p1) {
 #define M(q) case q: em::em_long_colfwd_paired_kernel<q><<<grid, 128, long_pair_smem(q), st>>>(cp); break;
     FOR_EACH_P1(M)
@@ -380,6 +417,7 @@ int launch_long_colfwd_paired(proton_em_ctx* ctx, cudaStream_t st, int p1, const
 
 int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int p1, bool blue, const em::ColParams& cp, int groups) {
   const dim3 grid(kLongColBlocks, groups);
+  ProfScope prof(ctx, PK_LONG_COLINV, st);
   switch (p1) {
 #define M(q)                                                                                              \
   case q:                                                                                                 \
@@ -397,6 +435,7 @@ int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int p1, bool blue, c
 
 int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::LongWave& w, int maxN) {
   const dim3 grid(std::min(256, (maxN + 255) / 256), w.n_tr);
+  ProfScope prof(ctx, PK_LONG_SCATTER, st);
   switch (p1) {
 #define M(q) case (1 << q): em::em_long_scatter_kernel<q><<<grid, 256, 0, st>>>(w); break;
     FOR_EACH_LOG2P1(M)
@@ -410,6 +449,7 @@ int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::L
 
 int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp, int n_tr) {
   const dim3 grid(rp.p1, n_tr);
+  ProfScope prof(ctx, PK_LONG_ROW, st);
   em::em_long_row_kernel<<<grid, em::kLongRowThreads, kLongRowSmem, st>>>(rp);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
@@ -650,6 +690,8 @@ int proton_em_destroy(proton_em_ctx* ctx) {
     if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
   }
   if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+  for (const proton_em_ctx::ProfRec& r : ctx->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (cudaEvent_t e : ctx->prof_pool) cudaEventDestroy(e);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   for (int i = 0; i < 2; ++i) {
     if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
@@ -677,6 +719,33 @@ int proton_em_synchronize(proton_em_ctx* ctx) {
 
 void* proton_em_stream(proton_em_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 int64_t proton_em_launch_count(const proton_em_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int proton_em_profile(proton_em_ctx* ctx, int enable) {
+  if (!ctx) return fail(PROTON_EM_EINVAL, "proton_em_profile: ctx is NULL");
+  { int rc = set_device(ctx); if (rc) return rc; }
+  CU_TRY(cudaDeviceSynchronize());
+  // fold the finished records into the totals and recycle their events
+  for (const proton_em_ctx::ProfRec& r : ctx->prof_recs) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { ctx->prof_ms[r.kind] += ms; ctx->prof_n[r.kind]++; }
+    ctx->prof_pool.push_back(r.a);
+    ctx->prof_pool.push_back(r.b);
+  }
+  ctx->prof_recs.clear();
+  if (enable && !ctx->prof_on)
+    for (int k = 0; k < PK_COUNT; ++k) { ctx->prof_ms[k] = 0.0; ctx->prof_n[k] = 0; }
+  ctx->prof_on = enable != 0;
+  return PROTON_EM_OK;
+}
+
+int proton_em_profile_read(const proton_em_ctx* ctx, int kind, const char** name, double* total_ms, int64_t* launches) {
+  if (!ctx) return fail(PROTON_EM_EINVAL, "proton_em_profile_read: ctx is NULL");
+  if (kind < 0 || kind >= PK_COUNT) return fail(PROTON_EM_EINVAL, "kernel kind %d out of range [0, %d)", kind, (int)PK_COUNT);
+  if (name) *name = kProfNames[kind];
+  if (total_ms) *total_ms = ctx->prof_ms[kind];
+  if (launches) *launches = ctx->prof_n[kind];
+  return PROTON_EM_OK;
+}
 
 int proton_em_plan_destroy(proton_em_plan* plan) {
   if (plan && plan->ctx) { cudaSetDevice(plan->ctx->device); cudaStreamSynchronize(plan->ctx->stream); }
@@ -982,7 +1051,10 @@ static int eval_long_finish(proton_em_plan* p, long long n_tr_total, int T, doub
   w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
   w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
   w.critical = critical;
-  em::em_long_reduce_kernel<<<(unsigned)((2 * n_tr_total + 127) / 128), 128, 0, ctx->stream>>>(w, kLongColBlocks);
+  {
+    ProfScope prof(ctx, PK_LONG_REDUCE, ctx->stream);
+    em::em_long_reduce_kernel<<<(unsigned)((2 * n_tr_total + 127) / 128), 128, 0, ctx->stream>>>(w, kLongColBlocks);
+  }
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   return PROTON_EM_OK;
@@ -1046,9 +1118,12 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
                              d_stress, d_mx, d_amx, d_flag, critical, maxN};
           const size_t smem = (size_t)(4 * maxN + ((maxN + 7) / 8) * ((maxN + 3) / 4) * 32) * sizeof(double);
           const unsigned items = (unsigned)((long long)cnt * chunks);
-          if (maxN > 64) em::em_eval_dense_kernel<12><<<items, 128, smem, cst>>>(sp);
-          else if (maxN > 32) em::em_eval_dense_kernel<8><<<items, 128, smem, cst>>>(sp);
-          else em::em_eval_dense_kernel<4><<<items, 128, smem, cst>>>(sp);
+          {
+            ProfScope prof(ctx, PK_DENSE, cst);
+            if (maxN > 64) em::em_eval_dense_kernel<12><<<items, 128, smem, cst>>>(sp);
+            else if (maxN > 32) em::em_eval_dense_kernel<8><<<items, 128, smem, cst>>>(sp);
+            else em::em_eval_dense_kernel<4><<<items, 128, smem, cst>>>(sp);
+          }
           ctx->launches++;
           CU_TRY(cudaGetLastError());
           begin = end;
@@ -1062,7 +1137,10 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
                          p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_exp,
                          d_stress, d_mx, d_amx, d_flag, critical, 0};
       const long long items = (long long)cl.count * chunks;
-      em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, cst>>>(sp);
+      {
+        ProfScope prof(ctx, PK_TABLE, cst);
+        em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, cst>>>(sp);
+      }
       ctx->launches++;
       CU_TRY(cudaGetLastError());
       continue;

@@ -130,6 +130,16 @@ def synthetic_ragged(num_lines: int, seed: int = 0, nmin: int = 16, nmax: int = 
     return LineBatch(N.astype(np.int32), a, trip_off, rows, cols, vals, u_off, curden)
 
 
+def kernel_class(n: int, dense_max: int = 88) -> str:
+    """Which kernel family evaluates a line of n nodes (mirror of classify() in csrc/proton_em.cu)."""
+    pow2 = n & (n - 1) == 0
+    if n <= dense_max and not (pow2 and n >= 64):
+        return "dense"
+    if pow2:
+        return "fft_pow2" if n <= 8192 else "long_pow2"
+    return "fft_blue" if n <= 4096 else "long_blue"
+
+
 def partition_lines(num_nodes: np.ndarray, world: int, T: int = 1) -> List[np.ndarray]:
     """Segment-balanced static split over `world` GPUs (BASELINE north_star): longest-processing-
     time-first on the cost N * (1 + 0.12 log2 N); returns, per rank, the sorted line indices it owns."""
