@@ -176,8 +176,9 @@ struct proton_em_ctx {
   int64_t launches = 0;
   // long-line path: column twiddles per P1 and the wave scratch (grown on demand, reused by every call)
   em::cplx* d_twl[em::kLongMaxP1 + 1] = {};   // column twiddles per P1
-  static constexpr int kLanes = 8;          // up to 8 streams; `lanes` of them are used (PROTON_EM_LANES, default 3)
-  int lanes = 3;
+  static constexpr int kLanes = 8;          // up to 8 streams; `lanes` of them are used (PROTON_EM_LANES, default 2:
+                                            // two 32 MB waves in flight measured best, the scratch stays well inside L2)
+  int lanes = 2;
   cudaStream_t lane[kLanes] = {};
   cudaEvent_t ev_fork = nullptr, ev_join[kLanes] = {};
   // host-buffer path (proton_em_analyze_host): cached device staging, a copy stream, per-buffer events
