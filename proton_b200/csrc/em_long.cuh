@@ -363,9 +363,18 @@ __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) 
   const double t2 = (2 * pr + 1 < w.T) ? w.ts[2 * pr + 1] : t1;
   const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
   cplx* x = w.x + (long long)s * P;
-  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < N; k += gridDim.x * blockDim.x) {
-    const cplx z = long_zk(tab.lam, W, k, N, w1, t1, w2, t2);
-    x[long_pos<LOG2P1>(k)] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
+  // one thread per mode pair (k, N-k): the four modal values serve both packed entries
+  const double* __restrict__ lam = tab.lam;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; 2 * k <= N; k += gridDim.x * blockDim.x) {
+    const double l = lam[k], wk = W[k];
+    const double y1 = em_modal(l, wk, w1, t1, nullptr), y2 = em_modal(l, wk, w2, t2, nullptr);
+    if (k == 0) { x[long_pos<LOG2P1>(0)] = cplx{y1, y2}; continue; }
+    const int kk = N - k;
+    if (kk == k) { x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(tab.pre + k), cplx{y1 + y2, y2 - y1}); continue; }
+    const double lm = lam[kk], wm = W[kk];
+    const double m1 = em_modal(lm, wm, w1, t1, nullptr), m2 = em_modal(lm, wm, w2, t2, nullptr);
+    x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(tab.pre + k), cplx{y1 + m2, y2 - m1});
+    x[long_pos<LOG2P1>(kk)] = cmul(ldg_cplx(tab.pre + kk), cplx{m1 + y2, m2 - y1});
   }
 }
 

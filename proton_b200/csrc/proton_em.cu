@@ -435,7 +435,7 @@ int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int p1, bool blue, c
 }
 
 int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::LongWave& w, int maxN) {
-  const dim3 grid(std::min(256, (maxN + 255) / 256), w.n_tr);
+  const dim3 grid(std::min(256, (maxN / 2 + 256) / 256), w.n_tr);     // one thread per mode pair (k, N-k)
   ProfScope prof(ctx, PK_LONG_SCATTER, st);
   switch (p1) {
 #define M(q) case (1 << q): em::em_long_scatter_kernel<q><<<grid, 256, 0, st>>>(w); break;

@@ -199,6 +199,31 @@ def test_edge_inputs(ctx, oracle):
     assert r.max_stress.shape == (0, 3)
 
 
+def test_per_kernel_profile_counts_the_launches(ctx):
+    """proton_em_profile: every launch of the evaluation path is timed on its own stream (bench.py's roofline)."""
+    rng = np.random.default_rng(11)
+    batch = synth_batch(rng, [5, 40, 64, 300, 1000, 5000])
+    ts = np.logspace(6, 8, 4)
+    plan = ctx.pack(batch)
+    plan.eval(ts, critical=1e8)
+    before = ctx.launch_count
+    ctx.profile(True)
+    got = plan.eval(ts, critical=1e8)
+    ctx.profile(False)
+    launched = ctx.launch_count - before
+    prof = ctx.profile_read()
+    assert sum(n for _ms, n in prof.values()) == launched
+    for name in ("em_eval_dense_kernel", "em_eval_fft_kernel<pow2>", "em_eval_fft_kernel<bluestein>",
+                 "em_long_colfwd_paired_kernel", "em_long_row_kernel", "em_long_colinv_kernel", "em_long_reduce_kernel"):
+        ms, n = prof[name]
+        assert n >= 1 and 0.0 < ms < 1e3, (name, ms, n)
+    # timing does not change results, and the totals stay readable until the next profile(True)
+    again = plan.eval(ts, critical=1e8)
+    assert np.array_equal(again.stress, got.stress)
+    assert ctx.profile_read() == prof
+    plan.close()
+
+
 def test_errors_are_reported_not_swallowed(ctx):
     from proton_b200.api import LineBatch, ProtonEmError
     rng = np.random.default_rng(5)
