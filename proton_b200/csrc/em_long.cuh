@@ -123,6 +123,13 @@ template <int R, int SIGN> struct DftAny {
   }
 };
 
+// Programmatic dependent launch (PDL): the three kernels of a wave run back to back on one stream.  Each lets the
+// next one start its CTAs as soon as all of its own are resident (pdl_launch_dependents at entry) and blocks only
+// where it first touches what its predecessor produced or still reads (pdl_wait).  Without the launch attribute both
+// instructions are no-ops.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 struct LongWave {
   // transforms of this wave: slot s -> (line, timestamp pair)
   const int* tr_line;
@@ -269,6 +276,7 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
   cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][128]   w_P^{-j r} of this thread's column
   cplx* ys = twt + P1 * 128;                              // [QMAX][128] modal pairs (Yhat1, Yhat2) of this thread's modes
   const int tid = threadIdx.x;
+  pdl_launch_dependents();
   const int a = blockIdx.x * 64 + (tid & 63);
   const int side = tid >> 6;
   int prev_c = -1, j = 0, partner = tid;
@@ -331,6 +339,7 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
       }
     }
     __syncthreads();
+    if (s == s0) pdl_wait();       // the scratch may still be read by the previous wave's inverse column pass
     if (active) {
       DftAny<P1, -1>::run(v);
       cplx* x = p.w.x + (long long)s * P;
@@ -363,6 +372,8 @@ __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) 
   const double t2 = (2 * pr + 1 < w.T) ? w.ts[2 * pr + 1] : t1;
   const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
   cplx* x = w.x + (long long)s * P;
+  pdl_launch_dependents();
+  pdl_wait();
   // one thread per mode pair (k, N-k): the four modal values serve both packed entries
   const double* __restrict__ lam = tab.lam;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; 2 * k <= N; k += gridDim.x * blockDim.x) {
@@ -442,9 +453,11 @@ __global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_lo
   cplx* data = twb + stage_tw_total(LOG2P);
   const int tid = threadIdx.x;
   const int r = blockIdx.x, s = blockIdx.y;
+  pdl_launch_dependents();
   for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = p.tw[i];
   const long long P = (long long)P2 * p.p1;
   cplx* row = p.x + (long long)s * P + (long long)r * P2;
+  pdl_wait();                                         // the row comes from the preceding column / scatter kernel
   if (p.mode != 2) {
     __syncthreads();                                  // twiddles in place
     row_dif_from_global<NT>(row, data, twb, tid);
@@ -479,10 +492,12 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
   __shared__ double red_v[2][kLongColsPerCta / 32];
   __shared__ int red_i[2][kLongColsPerCta / 32];
   const int j = blockIdx.x * kLongColsPerCta + threadIdx.x;
+  pdl_launch_dependents();
   for (int r = 1; r < P1; ++r) twt[r * kLongColsPerCta + threadIdx.x] = ldg_cplx(p.twl + (long long)r * P2 + j);
   const int s0 = blockIdx.y * p.tr_per_cta;
   const int s1 = min(p.w.n_tr, s0 + p.tr_per_cta);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  pdl_wait();                                         // x is the row kernel's output
   const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
   for (int s = s0; s < s1; ++s) {
     const int line = p.w.tr_line[s], pr = p.w.tr_pair[s];

@@ -389,6 +389,22 @@ int ensure_long(proton_em_ctx* ctx, int p1, int cap, long long n_tr_total) {
   return PROTON_EM_OK;
 }
 
+// Launch with the programmatic-stream-serialization attribute (PDL, see em_long.cuh); PROTON_EM_PDL=0 turns it off.
+bool pdl_enabled() {
+  static const bool v = [] { const char* e = std::getenv("PROTON_EM_PDL"); return !(e && std::atoi(e) == 0); }();
+  return v;
+}
+template <typename Param>
+cudaError_t launch_pdl(void (*kern)(const Param), dim3 grid, unsigned block, size_t smem, cudaStream_t st, const Param& prm) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, prm);
+}
+
 int launch_long_colfwd(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::ColParams& cp, int groups) {
   const dim3 grid(kLongColBlocks, groups);
   switch (p1) {
@@ -406,7 +422,7 @@ int launch_long_colfwd_paired(proton_em_ctx* ctx, cudaStream_t st, int p1, const
   const dim3 grid(em::kLongPairBlocks, groups);
   ProfScope prof(ctx, PK_LONG_COLFWD, st);
   switch (p1) {
-#define M(q) case q: em::em_long_colfwd_paired_kernel<q><<<grid, 128, long_pair_smem(q), st>>>(cp); break;
+#define M(q) case q: CU_TRY(launch_pdl(em::em_long_colfwd_paired_kernel<q>, grid, 128, long_pair_smem(q), st, cp)); break;
     FOR_EACH_P1(M)
 #undef M
     default: return fail(PROTON_EM_EINVAL, "unsupported row count %d", p1);
@@ -422,8 +438,8 @@ int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int p1, bool blue, c
   switch (p1) {
 #define M(q)                                                                                              \
   case q:                                                                                                 \
-    if (blue) em::em_long_colinv_kernel<q, true><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp); \
-    else em::em_long_colinv_kernel<q, false><<<grid, em::kLongColsPerCta, long_col_smem(q), st>>>(cp);     \
+    if (blue) CU_TRY(launch_pdl(em::em_long_colinv_kernel<q, true>, grid, em::kLongColsPerCta, long_col_smem(q), st, cp)); \
+    else CU_TRY(launch_pdl(em::em_long_colinv_kernel<q, false>, grid, em::kLongColsPerCta, long_col_smem(q), st, cp));     \
     break;
     FOR_EACH_P1(M)
 #undef M
@@ -438,7 +454,7 @@ int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::L
   const dim3 grid(std::min(256, (maxN / 2 + 256) / 256), w.n_tr);     // one thread per mode pair (k, N-k)
   ProfScope prof(ctx, PK_LONG_SCATTER, st);
   switch (p1) {
-#define M(q) case (1 << q): em::em_long_scatter_kernel<q><<<grid, 256, 0, st>>>(w); break;
+#define M(q) case (1 << q): CU_TRY(launch_pdl(em::em_long_scatter_kernel<q>, grid, 256, 0, st, w)); break;
     FOR_EACH_LOG2P1(M)
 #undef M
     default: return fail(PROTON_EM_EINVAL, "unsupported row count %d", p1);
@@ -451,7 +467,7 @@ int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::L
 int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp, int n_tr) {
   const dim3 grid(rp.p1, n_tr);
   ProfScope prof(ctx, PK_LONG_ROW, st);
-  em::em_long_row_kernel<<<grid, em::kLongRowThreads, kLongRowSmem, st>>>(rp);
+  CU_TRY(launch_pdl(em::em_long_row_kernel, grid, em::kLongRowThreads, kLongRowSmem, st, rp));
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   return PROTON_EM_OK;
