@@ -84,15 +84,18 @@ template <int SIGN> struct Dft<8, SIGN> {
     cplx o[4] = {v[1], v[3], v[5], v[7]};
     Dft<4, SIGN>::run(e);
     Dft<4, SIGN>::run(o);
+    // o1 * e^{SIGN i pi/4} and o3 * e^{SIGN 3 i pi/4}: the factor 1/sqrt(2) rides on the final add as an FMA
     constexpr double h = 0.70710678118654752440;
     constexpr double s = (double)SIGN;
-    const cplx o1 = cplx{(o[1].x - s * o[1].y) * h, (s * o[1].x + o[1].y) * h};
+    const cplx t1 = cplx{o[1].x - s * o[1].y, s * o[1].x + o[1].y};
     const cplx o2 = mul_i<SIGN>(o[2]);
-    const cplx o3 = cplx{(-o[3].x - s * o[3].y) * h, (s * o[3].x - o[3].y) * h};
+    const cplx t3 = cplx{-o[3].x - s * o[3].y, s * o[3].x - o[3].y};
     v[0] = cadd(e[0], o[0]); v[4] = csub(e[0], o[0]);
-    v[1] = cadd(e[1], o1);   v[5] = csub(e[1], o1);
+    v[1] = cplx{fma(h, t1.x, e[1].x), fma(h, t1.y, e[1].y)};
+    v[5] = cplx{fma(-h, t1.x, e[1].x), fma(-h, t1.y, e[1].y)};
     v[2] = cadd(e[2], o2);   v[6] = csub(e[2], o2);
-    v[3] = cadd(e[3], o3);   v[7] = csub(e[3], o3);
+    v[3] = cplx{fma(h, t3.x, e[3].x), fma(h, t3.y, e[3].y)};
+    v[7] = cplx{fma(-h, t3.x, e[3].x), fma(-h, t3.y, e[3].y)};
   }
 };
 
@@ -125,11 +128,16 @@ __host__ __device__ constexpr int stage_tw_offset(int log2p, int i) {
 }
 __host__ __device__ constexpr int stage_tw_total(int log2p) { return stage_tw_offset(log2p, plan_n(log2p)); }
 
-// w[q] = w1^q for q = 1..R-1 (w[0] unused).
+// w[q] = w1^q for q = 1..R-1 (w[0] unused).  |w1| = 1, so w^{q+1} = 2 Re(w1) w^q - w^{q-1}: two FMAs per power
+// (error growth is bounded by the Chebyshev polynomials U_q <= q + 1, i.e. a few ulp for q <= 7).
 template <int RADIX> __device__ __forceinline__ void tw_powers(cplx w1, cplx (&w)[RADIX]) {
   w[1] = w1;
-  if constexpr (RADIX >= 4) { w[2] = cmul(w1, w1); w[3] = cmul(w[2], w1); }
-  if constexpr (RADIX >= 8) { w[4] = cmul(w[2], w[2]); w[5] = cmul(w[4], w1); w[6] = cmul(w[4], w[2]); w[7] = cmul(w[4], w[3]); }
+  if constexpr (RADIX >= 4) {
+    const double tx = w1.x + w1.x;
+    w[2] = cplx{fma(tx, w1.x, -1.0), tx * w1.y};
+#pragma unroll
+    for (int q = 3; q < RADIX; ++q) w[q] = cplx{fma(tx, w[q - 1].x, -w[q - 2].x), fma(tx, w[q - 1].y, -w[q - 2].y)};
+  }
 }
 
 // Shared-memory index padding (units of 16-byte complex): one pad slot per 8 elements keeps the
@@ -251,14 +259,14 @@ __device__ __forceinline__ void fft_stage0_pruned(cplx* __restrict__ data, int g
       const cplx e0 = cadd(v0, v2), e2 = csub(v0, v2), e1 = cadd(v0, i2), e3 = csub(v0, i2);
       const cplx o0 = cadd(v1, v3), o2 = csub(v1, v3), o1 = cadd(v1, i3), o3 = csub(v1, i3);
       constexpr double h = 0.70710678118654752440;
-      const cplx r1 = cplx{(o1.x + o1.y) * h, (o1.y - o1.x) * h};      // o1 * e^{-i pi/4}
+      const cplx r1 = cplx{o1.x + o1.y, o1.y - o1.x};                  // o1 * e^{-i pi/4} * sqrt(2)
       const cplx r2 = mul_i<-1>(o2);
-      const cplx r3 = cplx{(o3.y - o3.x) * h, (-o3.x - o3.y) * h};     // o3 * e^{-3 i pi/4}
+      const cplx r3 = cplx{o3.y - o3.x, -o3.x - o3.y};                 // o3 * e^{-3 i pi/4} * sqrt(2)
       cplx v[8];
       v[0] = cadd(e0, o0); v[4] = csub(e0, o0);
-      v[1] = cadd(e1, r1); v[5] = csub(e1, r1);
+      v[1] = cplx{fma(h, r1.x, e1.x), fma(h, r1.y, e1.y)}; v[5] = cplx{fma(-h, r1.x, e1.x), fma(-h, r1.y, e1.y)};
       v[2] = cadd(e2, r2); v[6] = csub(e2, r2);
-      v[3] = cadd(e3, r3); v[7] = csub(e3, r3);
+      v[3] = cplx{fma(h, r3.x, e3.x), fma(h, r3.y, e3.y)}; v[7] = cplx{fma(-h, r3.x, e3.x), fma(-h, r3.y, e3.y)};
 #pragma unroll
       for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
 #pragma unroll
