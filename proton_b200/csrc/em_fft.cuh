@@ -99,12 +99,63 @@ template <int SIGN> struct Dft<8, SIGN> {
   }
 };
 
+// cos(2 pi m / 32), m in [0, 32)
+__host__ __device__ constexpr double cos32(int m) {
+  m &= 31;
+  if (m > 16) m = 32 - m;            // cos is even around 16
+  const bool neg = m > 8;
+  if (neg) m = 16 - m;
+  const double c = m == 0 ? 1.0 : m == 1 ? 0.98078528040323044913 : m == 2 ? 0.92387953251128675613
+                   : m == 3 ? 0.83146961230254523708 : m == 4 ? 0.70710678118654752440
+                   : m == 5 ? 0.55557023301960222474 : m == 6 ? 0.38268343236508977173
+                   : m == 7 ? 0.19509032201612826785 : 0.0;
+  return neg ? -c : c;
+}
+__host__ __device__ constexpr double sin32(int m) { return cos32(m - 8); }
+
+// Radix-2 recursion on top of Dft<8>: natural order in and out.
+template <int R, int SIGN> struct DftBig {
+  static __device__ __forceinline__ void run(cplx (&v)[R]) {
+    if constexpr (R <= 8) {
+      Dft<R, SIGN>::run(v);
+    } else {
+      cplx e[R / 2], o[R / 2];
+#pragma unroll
+      for (int i = 0; i < R / 2; ++i) { e[i] = v[2 * i]; o[i] = v[2 * i + 1]; }
+      DftBig<R / 2, SIGN>::run(e);
+      DftBig<R / 2, SIGN>::run(o);
+#pragma unroll
+      for (int r = 0; r < R / 2; ++r) {
+        cplx t;
+        if (r == 0) t = o[r];
+        else if (4 * r == R) t = mul_i<SIGN>(o[r]);
+        else {
+          const double c = cos32(r * (32 / R)), s = (double)SIGN * sin32(r * (32 / R));
+          t = cplx{o[r].x * c - o[r].y * s, o[r].x * s + o[r].y * c};
+        }
+        v[r] = cadd(e[r], t);
+        v[r + R / 2] = csub(e[r], t);
+      }
+    }
+  }
+};
+template <int SIGN> struct Dft<16, SIGN> {
+  static __device__ __forceinline__ void run(cplx (&v)[16]) { DftBig<16, SIGN>::run(v); }
+};
+
 // ---- stage plans: radices in DIF order (largest stride first); the first radix is always 8 --------
 __host__ __device__ constexpr int lg2(int r) { return r == 2 ? 1 : r == 4 ? 2 : r == 8 ? 3 : 4; }
-// LOG2P = 3*n8 + rem: n8 radix-8 stages followed by one radix-2 (rem 1) or radix-4 (rem 2) stage.
-__host__ __device__ constexpr int plan_n(int log2p) { return log2p / 3 + (log2p % 3 ? 1 : 0); }
+// LOG2P = 3*n8 + rem: n8 radix-8 stages followed by one radix-2 (rem 1) or radix-4 (rem 2) stage.  The 4096-point
+// transform (in-CTA p = 12 classes and the rows of the long path) runs as 16 x 16 x 16 instead: 8 instead of 12 sweeps
+// over shared memory, which is the busiest pipe of these kernels; a radix-16 butterfly keeps 64 data
+// registers per thread, so those kernels run 256 threads per CTA.
+#ifndef EM_RADIX16_P12
+#define EM_RADIX16_P12 1
+#endif
+__host__ __device__ constexpr bool plan16(int log2p) { return EM_RADIX16_P12 != 0 && log2p == 12; }
+__host__ __device__ constexpr int plan_n(int log2p) { return plan16(log2p) ? log2p / 4 : log2p / 3 + (log2p % 3 ? 1 : 0); }
 __host__ __device__ constexpr int plan_radix(int log2p, int i) {
-  return i < log2p / 3 ? 8 : (log2p % 3 == 1 ? 2 : 4);
+  return plan16(log2p) ? 16 : (i < log2p / 3 ? 8 : (log2p % 3 == 1 ? 2 : 4));
 }
 template <int LOG2P, int I> __host__ __device__ constexpr int stage_radix() { return plan_radix(LOG2P, I); }
 template <int LOG2P, int I> __host__ __device__ constexpr int stage_log2s() {
@@ -140,11 +191,27 @@ template <int RADIX> __device__ __forceinline__ void tw_powers(cplx w1, cplx (&w
   }
 }
 
-// Shared-memory index padding (units of 16-byte complex): one pad slot per 8 elements keeps the
-// stride-R accesses of the s = 1 stages conflict-free, one more per P/8 elements does the same for the
-// digit-reversed scatter of the power-of-two path.
-template <int LOG2P> __host__ __device__ constexpr int pad_idx(int p) { return p + (p >> 3) + (p >> (LOG2P - 3)); }
-template <int LOG2P> __host__ __device__ constexpr int padded_len() { return (1 << LOG2P) + (1 << (LOG2P - 3)) + 8; }
+// v[q] *= w^q (q = 1..R-1), w = (tv.x, SIGN tv.y): the same recurrence, nothing kept (radix 16 has no registers to spare).
+template <int RADIX, int SIGN> __device__ __forceinline__ void twiddle_jit(cplx (&v)[RADIX], cplx tv) {
+  const double tx = tv.x + tv.x;
+  cplx wp = cplx{1.0, 0.0}, wc = cplx{tv.x, SIGN > 0 ? tv.y : -tv.y};
+  v[1] = cmul(v[1], wc);
+#pragma unroll
+  for (int q = 2; q < RADIX; ++q) {
+    const cplx wn = cplx{fma(tx, wc.x, -wp.x), fma(tx, wc.y, -wp.y)};
+    v[q] = cmul(v[q], wn);
+    wp = wc; wc = wn;
+  }
+}
+
+// Shared-memory index padding (units of 16-byte complex): one pad slot per 8 (16 when the innermost radix is 16)
+// elements keeps the stride-R accesses of the s = 1 stages conflict-free, one more per P/R0 elements does the same
+// for the digit-reversed scatter of the power-of-two path (checked by brute force for every plan).
+__host__ __device__ constexpr int pad_sh1(int log2p) { return plan_radix(log2p, plan_n(log2p) - 1) == 16 ? 4 : 3; }
+__host__ __device__ constexpr int pad_sh2(int log2p) { return log2p - lg2(plan_radix(log2p, 0)); }
+__host__ __device__ constexpr int pad_idx_rt(int log2p, int p) { return p + (p >> pad_sh1(log2p)) + (p >> pad_sh2(log2p)); }
+template <int LOG2P> __host__ __device__ constexpr int pad_idx(int p) { return pad_idx_rt(LOG2P, p); }
+template <int LOG2P> __host__ __device__ constexpr int padded_len() { return (pad_idx_rt(LOG2P, (1 << LOG2P) - 1) + 8) & ~7; }
 
 // Padded offset of element q of a butterfly relative to its first element: for every stage of the plans above it
 // does not depend on the butterfly, so shared-memory accesses use immediate offsets.
@@ -175,7 +242,7 @@ template <int LOG2P, bool BLUE> struct Cfg {
 #ifndef EM_G10
 #define EM_G10 2
 #endif
-  static constexpr int NT = LOG2P >= 13 ? 1024 : LOG2P == 12 ? 512 : EM_NT_MID;
+  static constexpr int NT = LOG2P >= 13 ? 1024 : LOG2P == 12 ? (plan16(12) ? 256 : 512) : EM_NT_MID;
   // rows of the staging buffer: N <= P (pow2) or N <= P/2 + 1 (Bluestein)
   static constexpr int NSTAGE = BLUE ? (P / 2 + 8) : P;
   static constexpr int G = LOG2P <= 6 ? 32 : LOG2P == 7 ? 16 : LOG2P == 8 ? 8 : LOG2P == 9 ? 4 : LOG2P == 10 ? EM_G10 : 1;
@@ -199,12 +266,33 @@ __device__ __forceinline__ void fft_stage(cplx* __restrict__ data, int gcount, c
   for (int b = (NB < NT ? tid % NB : tid); b < NB; b += BSTEP) {
     const int j = b & (S - 1);
     const int base = ((b >> LOG2S) << (LOG2S + LOG2R)) | j;
+    const int pbase = pad_idx<LOG2P>(base);
+    if constexpr (RADIX == 16) {
+      // no room for a table of powers next to 16 complex values: twiddles are formed as they are applied
+      cplx tv = cplx{1.0, 0.0};
+      if (S > 1) tv = tw[TWOFF + j];
+      for (int g = g0; g < gcount; g += GSTEP) {
+        cplx* d = data + g * TSTRIDE + pbase;
+        cplx v[RADIX];
+#pragma unroll
+        for (int q = 0; q < RADIX; ++q) v[q] = d[pad_off<LOG2P, LOG2S>(q)];
+        if (DIF) {
+          Dft<RADIX, SIGN>::run(v);
+          if (S > 1) twiddle_jit<RADIX, SIGN>(v, tv);
+        } else {
+          if (S > 1) twiddle_jit<RADIX, SIGN>(v, tv);
+          Dft<RADIX, SIGN>::run(v);
+        }
+#pragma unroll
+        for (int q = 0; q < RADIX; ++q) d[pad_off<LOG2P, LOG2S>(q)] = v[q];
+      }
+      continue;
+    }
     cplx w[RADIX];
     if (S > 1) {
       const cplx tv = tw[TWOFF + j];
       tw_powers<RADIX>(cplx{tv.x, SIGN > 0 ? tv.y : -tv.y}, w);
     }
-    const int pbase = pad_idx<LOG2P>(base);
     for (int g = g0; g < gcount; g += GSTEP) {
       cplx* d = data + g * TSTRIDE + pbase;
       cplx v[RADIX];
@@ -229,18 +317,44 @@ __device__ __forceinline__ void fft_stage(cplx* __restrict__ data, int gcount, c
   }
 }
 
-// First DIF stage of Bluestein (radix 8, stride P/8) with the zero padding never materialised: the chirped
-// spectrum occupies positions < N <= P/2, so butterfly inputs 4..7 are zero and inputs 0..3 are read only where
-// they fall below N.  Saves the zero-fill pass and half of this stage's shared-memory reads.
+// First DIF stage of Bluestein (radix R0, stride P/R0) with the zero padding never materialised: the chirped
+// spectrum occupies positions < N <= P/2, so the upper half of the butterfly inputs is zero and the lower half is read
+// only where it falls below N.  Saves the zero-fill pass and half of this stage's shared-memory reads.
 template <int LOG2P, int NT>
 __device__ __forceinline__ void fft_stage0_pruned(cplx* __restrict__ data, int gcount, const cplx* __restrict__ tw,
                                                   int tid, int n_valid) {
-  constexpr int P = 1 << LOG2P, LOG2S = LOG2P - 3, S = 1 << LOG2S, NB = S;
-  static_assert(plan_radix(LOG2P, 0) == 8, "first stage is radix 8");
+  constexpr int R0 = plan_radix(LOG2P, 0);
+  constexpr int LOG2S = LOG2P - lg2(R0), S = 1 << LOG2S, NB = S;
   constexpr int BSTEP = NB < NT ? NB : NT;
   constexpr int GSTEP = NB < NT ? NT / NB : 1;
   constexpr int TSTRIDE = padded_len<LOG2P>();
   const int g0 = NB < NT ? tid / NB : 0;
+  if constexpr (R0 == 16) {
+    // inputs 8..15 are zero: X[2r] = DFT_8(x)[r], X[2r+1] = DFT_8(x_q w16^q)[r]
+    for (int j = (NB < NT ? tid % NB : tid); j < NB; j += BSTEP) {
+      const cplx tv = tw[j];
+      const int pbase = pad_idx<LOG2P>(j);
+      for (int g = g0; g < gcount; g += GSTEP) {
+        cplx* d = data + g * TSTRIDE + pbase;
+        cplx a[8], b[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          a[q] = (j + q * S < n_valid) ? d[pad_off<LOG2P, LOG2S>(q)] : cplx{0.0, 0.0};
+          const double c = cos32(2 * q), sn = -sin32(2 * q);
+          b[q] = q == 0 ? a[q] : cplx{a[q].x * c - a[q].y * sn, a[q].x * sn + a[q].y * c};
+        }
+        Dft<8, -1>::run(a);
+        Dft<8, -1>::run(b);
+        cplx v[16];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) { v[2 * r] = a[r]; v[2 * r + 1] = b[r]; }
+        twiddle_jit<16, -1>(v, tv);
+#pragma unroll
+        for (int q = 0; q < 16; ++q) d[pad_off<LOG2P, LOG2S>(q)] = v[q];
+      }
+    }
+    return;
+  }
   for (int j = (NB < NT ? tid % NB : tid); j < NB; j += BSTEP) {
     cplx w[8];
     const cplx tv = tw[j];
@@ -285,10 +399,25 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
   const int g0 = NB < NT ? tid / NB : 0;
   for (int b = (NB < NT ? tid % NB : tid); b < NB; b += BSTEP) {
     const int base = b * RADIX;
+    const int pbase = pad_idx<LOG2P>(base);
+    if constexpr (RADIX == 16) {
+      for (int g = g0; g < gcount; g += GSTEP) {
+        cplx* d = data + g * TSTRIDE + pbase;
+        cplx v[RADIX];
+#pragma unroll
+        for (int q = 0; q < RADIX; ++q) v[q] = d[q];
+        Dft<RADIX, -1>::run(v);
+#pragma unroll
+        for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], ldg_cplx(hhat + base + q));
+        Dft<RADIX, +1>::run(v);
+#pragma unroll
+        for (int q = 0; q < RADIX; ++q) d[q] = v[q];
+      }
+      continue;
+    }
     cplx h[RADIX];
 #pragma unroll
     for (int q = 0; q < RADIX; ++q) h[q] = ldg_cplx(hhat + base + q);
-    const int pbase = pad_idx<LOG2P>(base);
     for (int g = g0; g < gcount; g += GSTEP) {
       cplx* d = data + g * TSTRIDE + pbase;
       cplx v[RADIX];
@@ -426,10 +555,11 @@ em_eval_fft_kernel(const EvalParams prm) {
     } else {
       DitStages<LOG2P, NST - 1, 1, NT>::run(data, gcount, twb, tid);
     }
-    // ---- last DIT stage (radix 8, stride P/8) fused with chirp post-multiply + de-interleave ---
+    // ---- last DIT stage (radix R0, stride P/R0) fused with chirp post-multiply + de-interleave ---
     {
-      constexpr int S = P / 8, NB = P / 8;
-      constexpr int QN = BLUE ? 4 : 8;          // Bluestein: only outputs m < N <= P/2 are wanted
+      constexpr int R0 = plan_radix(LOG2P, 0), LOG2S0 = LOG2P - lg2(R0);
+      constexpr int S = P / R0, NB = P / R0;
+      constexpr int QN = BLUE ? R0 / 2 : R0;    // Bluestein: only outputs m < N <= P/2 are wanted
       if constexpr (!C::ALIAS_STAGE) {
         constexpr int BSTEP = NB < NT ? NB : NT;
         constexpr int GSTEP = NB < NT ? NT / NB : 1;
@@ -477,14 +607,11 @@ em_eval_fft_kernel(const EvalParams prm) {
 #pragma unroll
         for (int it = 0; it < ITERS; ++it) {
           const int j = tid + it * NT;
-          cplx v[8];
+          cplx v[R0];
 #pragma unroll
-          for (int q = 0; q < 8; ++q) v[q] = data[pad_idx<LOG2P>(j) + pad_off<LOG2P, LOG2P - 3>(q)];
-          cplx w[8];
-          tw_powers<8>(twb[j], w);
-#pragma unroll
-          for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
-          Dft<8, +1>::run(v);
+          for (int q = 0; q < R0; ++q) v[q] = data[pad_idx<LOG2P>(j) + pad_off<LOG2P, LOG2S0>(q)];
+          twiddle_jit<R0, +1>(v, twb[j]);
+          Dft<R0, +1>::run(v);
 #pragma unroll
           for (int q = 0; q < QN; ++q) {
             const int m = j + q * S;

@@ -23,51 +23,7 @@ namespace em {
 constexpr int kLongLog2P2 = 12;
 constexpr int kLongP2 = 1 << kLongLog2P2;
 constexpr int kLongColsPerCta = 128;
-#ifndef EM_ROW_NT
-#define EM_ROW_NT 512
-#endif
-constexpr int kLongRowThreads = EM_ROW_NT;
-
-// cos(2 pi m / 32), m in [0, 32)
-__host__ __device__ constexpr double cos32(int m) {
-  m &= 31;
-  if (m > 16) m = 32 - m;            // cos is even around 16
-  const bool neg = m > 8;
-  if (neg) m = 16 - m;
-  const double c = m == 0 ? 1.0 : m == 1 ? 0.98078528040323044913 : m == 2 ? 0.92387953251128675613
-                   : m == 3 ? 0.83146961230254523708 : m == 4 ? 0.70710678118654752440
-                   : m == 5 ? 0.55557023301960222474 : m == 6 ? 0.38268343236508977173
-                   : m == 7 ? 0.19509032201612826785 : 0.0;
-  return neg ? -c : c;
-}
-__host__ __device__ constexpr double sin32(int m) { return cos32(m - 8); }
-
-// Radix-2 recursion on top of Dft<8>: natural order in and out.
-template <int R, int SIGN> struct DftBig {
-  static __device__ __forceinline__ void run(cplx (&v)[R]) {
-    if constexpr (R <= 8) {
-      Dft<R, SIGN>::run(v);
-    } else {
-      cplx e[R / 2], o[R / 2];
-#pragma unroll
-      for (int i = 0; i < R / 2; ++i) { e[i] = v[2 * i]; o[i] = v[2 * i + 1]; }
-      DftBig<R / 2, SIGN>::run(e);
-      DftBig<R / 2, SIGN>::run(o);
-#pragma unroll
-      for (int r = 0; r < R / 2; ++r) {
-        cplx t;
-        if (r == 0) t = o[r];
-        else if (4 * r == R) t = mul_i<SIGN>(o[r]);
-        else {
-          const double c = cos32(r * (32 / R)), s = (double)SIGN * sin32(r * (32 / R));
-          t = cplx{o[r].x * c - o[r].y * s, o[r].x * s + o[r].y * c};
-        }
-        v[r] = cadd(e[r], t);
-        v[r + R / 2] = csub(e[r], t);
-      }
-    }
-  }
-};
+constexpr int kLongRowThreads = plan16(kLongLog2P2) ? 256 : 512;     // one butterfly of the outermost radix per thread
 
 // Twiddles of the small column DFTs whose length is not a power of two: kDftTw[P1][m] = e^{+2 pi i m / P1}
 // (filled by the host at context creation).  Indices are compile-time constants after unrolling, so the values
@@ -403,50 +359,42 @@ struct RowParams {
   const cplx* tw;          // per-stage twiddle tables of the 4096-point transform
 };
 
-// Outermost stage (stride P2/8) of the row transform with one side in global memory: the DIF form reads its
+// Outermost stage (stride P2/R0) of the row transform with one side in global memory: the DIF form reads its
 // butterfly inputs straight from the row (lanes read consecutive columns, so every access is a coalesced 512-byte
 // segment), the DIT form writes its outputs straight back.  Saves the staging pass through shared memory and one
 // CTA barrier at each end of the kernel.
 template <int NT>
 __device__ __forceinline__ void row_dif_from_global(const cplx* __restrict__ row, cplx* __restrict__ data,
                                                     const cplx* __restrict__ twb, int tid) {
-  constexpr int LOG2P = kLongLog2P2, LOG2S = LOG2P - 3, S = 1 << LOG2S;
-  static_assert(plan_radix(LOG2P, 0) == 8, "outermost stage is radix 8");
+  constexpr int LOG2P = kLongLog2P2, R0 = plan_radix(LOG2P, 0), LOG2S = LOG2P - lg2(R0), S = 1 << LOG2S;
   for (int j = tid; j < S; j += NT) {
-    cplx v[8];
+    cplx v[R0];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) v[q] = row[j + q * S];
-    Dft<8, -1>::run(v);
-    cplx w[8];
-    const cplx tv = twb[j];
-    tw_powers<8>(cplx{tv.x, -tv.y}, w);
-#pragma unroll
-    for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
+    for (int q = 0; q < R0; ++q) v[q] = row[j + q * S];
+    Dft<R0, -1>::run(v);
+    twiddle_jit<R0, -1>(v, twb[j]);
     cplx* d = data + pad_idx<LOG2P>(j);
 #pragma unroll
-    for (int q = 0; q < 8; ++q) d[pad_off<LOG2P, LOG2S>(q)] = v[q];
+    for (int q = 0; q < R0; ++q) d[pad_off<LOG2P, LOG2S>(q)] = v[q];
   }
 }
 template <int NT>
 __device__ __forceinline__ void row_dit_to_global(cplx* __restrict__ row, const cplx* __restrict__ data,
                                                   const cplx* __restrict__ twb, int tid) {
-  constexpr int LOG2P = kLongLog2P2, LOG2S = LOG2P - 3, S = 1 << LOG2S;
+  constexpr int LOG2P = kLongLog2P2, R0 = plan_radix(LOG2P, 0), LOG2S = LOG2P - lg2(R0), S = 1 << LOG2S;
   for (int j = tid; j < S; j += NT) {
     const cplx* d = data + pad_idx<LOG2P>(j);
-    cplx v[8];
+    cplx v[R0];
 #pragma unroll
-    for (int q = 0; q < 8; ++q) v[q] = d[pad_off<LOG2P, LOG2S>(q)];
-    cplx w[8];
-    tw_powers<8>(twb[j], w);
+    for (int q = 0; q < R0; ++q) v[q] = d[pad_off<LOG2P, LOG2S>(q)];
+    twiddle_jit<R0, +1>(v, twb[j]);
+    Dft<R0, +1>::run(v);
 #pragma unroll
-    for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
-    Dft<8, +1>::run(v);
-#pragma unroll
-    for (int q = 0; q < 8; ++q) row[j + q * S] = v[q];
+    for (int q = 0; q < R0; ++q) row[j + q * S] = v[q];
   }
 }
 
-__global__ void __launch_bounds__(kLongRowThreads, 1024 / kLongRowThreads) em_long_row_kernel(const RowParams p) {
+__global__ void __launch_bounds__(kLongRowThreads, 2) em_long_row_kernel(const RowParams p) {
   constexpr int LOG2P = kLongLog2P2, P2 = kLongP2, NT = kLongRowThreads, NST = plan_n(LOG2P);
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* twb = reinterpret_cast<cplx*>(smem_raw);

@@ -677,7 +677,7 @@ int proton_em_create(proton_em_ctx** out, int device) {
           q |= (kk & ((1 << lr) - 1)) << sh;
           kk >>= lr;
         }
-        pos[k] = q + (q >> 3) + (q >> (p - 3));
+        pos[k] = em::pad_idx_rt(p, q);
       }
       CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_pos[p]), P * sizeof(int)));
       CU_TRY(cudaMemcpy(ctx->d_pos[p], pos.data(), P * sizeof(int), cudaMemcpyHostToDevice));
