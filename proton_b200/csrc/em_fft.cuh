@@ -148,14 +148,18 @@ __host__ __device__ constexpr int lg2(int r) { return r == 2 ? 1 : r == 4 ? 2 : 
 // LOG2P = 3*n8 + rem: n8 radix-8 stages followed by one radix-2 (rem 1) or radix-4 (rem 2) stage.  The 4096-point
 // transform (in-CTA p = 12 classes and the rows of the long path) runs as 16 x 16 x 16 instead: 8 instead of 12 sweeps
 // over shared memory, which is the busiest pipe of these kernels; a radix-16 butterfly keeps 64 data
-// registers per thread, so those kernels run 256 threads per CTA.
-#ifndef EM_RADIX16_P12
-#define EM_RADIX16_P12 1
+// registers per thread, so those kernels run P/16 threads per CTA.
+#ifndef EM_RADIX16
+#define EM_RADIX16 1
 #endif
-__host__ __device__ constexpr bool plan16(int log2p) { return EM_RADIX16_P12 != 0 && log2p == 12; }
-__host__ __device__ constexpr int plan_n(int log2p) { return plan16(log2p) ? log2p / 4 : log2p / 3 + (log2p % 3 ? 1 : 0); }
+// p = 12: 16 x 16 x 16;  p = 13: 16 x 16 x 16 x 2.
+__host__ __device__ constexpr bool plan16(int log2p) { return EM_RADIX16 != 0 && (log2p == 12 || log2p == 13); }
+__host__ __device__ constexpr int plan_n(int log2p) {
+  return plan16(log2p) ? log2p / 4 + (log2p % 4 ? 1 : 0) : log2p / 3 + (log2p % 3 ? 1 : 0);
+}
 __host__ __device__ constexpr int plan_radix(int log2p, int i) {
-  return plan16(log2p) ? 16 : (i < log2p / 3 ? 8 : (log2p % 3 == 1 ? 2 : 4));
+  return plan16(log2p) ? (i < log2p / 4 ? 16 : (log2p % 4 == 1 ? 2 : log2p % 4 == 2 ? 4 : 8))
+                       : (i < log2p / 3 ? 8 : (log2p % 3 == 1 ? 2 : 4));
 }
 template <int LOG2P, int I> __host__ __device__ constexpr int stage_radix() { return plan_radix(LOG2P, I); }
 template <int LOG2P, int I> __host__ __device__ constexpr int stage_log2s() {
@@ -242,7 +246,7 @@ template <int LOG2P, bool BLUE> struct Cfg {
 #ifndef EM_G10
 #define EM_G10 2
 #endif
-  static constexpr int NT = LOG2P >= 13 ? 1024 : LOG2P == 12 ? (plan16(12) ? 256 : 512) : EM_NT_MID;
+  static constexpr int NT = LOG2P >= 13 ? (plan16(13) ? 512 : 1024) : LOG2P == 12 ? (plan16(12) ? 256 : 512) : EM_NT_MID;
   // rows of the staging buffer: N <= P (pow2) or N <= P/2 + 1 (Bluestein)
   static constexpr int NSTAGE = BLUE ? (P / 2 + 8) : P;
   static constexpr int G = LOG2P <= 6 ? 32 : LOG2P == 7 ? 16 : LOG2P == 8 ? 8 : LOG2P == 9 ? 4 : LOG2P == 10 ? EM_G10 : 1;
