@@ -86,6 +86,22 @@ template <int R, int SIGN> struct DftAny {
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// v[r] *= w^r for r = 1..R-1 (|w| = 1): w^2 by squaring, then two interleaved chains w^{r+2} = w^r w^2, so the
+// rounding error grows like r/2 ulp and no table of R twiddles per column has to come from memory.
+template <int R> __device__ __forceinline__ void col_twiddle(cplx (&v)[R], cplx w) {
+  if constexpr (R >= 2) v[1] = cmul(v[1], w);
+  if constexpr (R >= 3) {
+    const cplx w2 = cmul(w, w);
+    cplx a = w2, b = w;              // a = w^{2m}, b = w^{2m-1}
+    v[2] = cmul(v[2], a);
+#pragma unroll
+    for (int r = 3; r < R; ++r) {
+      if (r & 1) { b = cmul(b, w2); v[r] = cmul(v[r], b); }
+      else       { a = cmul(a, w2); v[r] = cmul(v[r], a); }
+    }
+  }
+}
+
 struct LongWave {
   // transforms of this wave: slot s -> (line, timestamp pair)
   const int* tr_line;
@@ -229,8 +245,8 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
   constexpr int P2 = kLongP2, QMAX = (P1 + 1) / 2 + 1;
   constexpr long long P = (long long)P1 * P2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][128]   w_P^{-j r} of this thread's column
-  cplx* ys = twt + P1 * 128;                              // [QMAX][128] modal pairs (Yhat1, Yhat2) of this thread's modes
+  cplx* ys = reinterpret_cast<cplx*>(smem_raw);           // [QMAX][128] modal pairs (Yhat1, Yhat2) of this thread's modes
+  cplx wbase = cplx{1.0, 0.0};                            // w_P^{-j} of this thread's column
   const int tid = threadIdx.x;
   pdl_launch_dependents();
   const int a = blockIdx.x * 64 + (tid & 63);
@@ -255,11 +271,10 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
         j = side == 0 ? (c / 2 + a) & (P2 - 1) : (c / 2 - a) & (P2 - 1);
         partner = self ? tid : (tid ^ 64);
       }
-      if (active)
-        for (int r = 1; r < P1; ++r) {
-          const cplx t = ldg_cplx(p.twl + (long long)r * P2 + j);
-          twt[r * 128 + tid] = cplx{t.x, -t.y};
-        }
+      if (active) {
+        const cplx t = ldg_cplx(p.twl + P2 + j);          // row r = 1 of the table: w_P^{+j}
+        wbase = cplx{t.x, -t.y};
+      }
     }
     const NTab tab = p.w.tabs[p.w.line_tab[line]];
     const double* W = p.w.W + p.w.node_off[line];
@@ -298,10 +313,10 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
     if (s == s0) pdl_wait();       // the scratch may still be read by the previous wave's inverse column pass
     if (active) {
       DftAny<P1, -1>::run(v);
+      col_twiddle<P1>(v, wbase);
       cplx* x = p.w.x + (long long)s * P;
-      x[j] = v[0];
 #pragma unroll
-      for (int r = 1; r < P1; ++r) x[(long long)r * P2 + j] = cmul(v[r], twt[r * 128 + tid]);
+      for (int r = 0; r < P1; ++r) x[(long long)r * P2 + j] = v[r];
     }
   }
 }
@@ -435,13 +450,11 @@ template <int P1, bool BLUE>
 __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const ColParams p) {
   constexpr int P2 = kLongP2;
   constexpr long long P = (long long)P1 * P2;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  cplx* twt = reinterpret_cast<cplx*>(smem_raw);          // [P1][cols]  w_P^{+j r}
   __shared__ double red_v[2][kLongColsPerCta / 32];
   __shared__ int red_i[2][kLongColsPerCta / 32];
   const int j = blockIdx.x * kLongColsPerCta + threadIdx.x;
   pdl_launch_dependents();
-  for (int r = 1; r < P1; ++r) twt[r * kLongColsPerCta + threadIdx.x] = ldg_cplx(p.twl + (long long)r * P2 + j);
+  const cplx wbase = ldg_cplx(p.twl + P2 + j);            // w_P^{+j}
   const int s0 = blockIdx.y * p.tr_per_cta;
   const int s1 = min(p.w.n_tr, s0 + p.tr_per_cta);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -454,9 +467,9 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
     const NTab tab = p.w.tabs[p.w.line_tab[line]];
     const cplx* x = p.w.x + (long long)s * P;
     cplx v[P1];
-    v[0] = x[j];
 #pragma unroll
-    for (int r = 1; r < P1; ++r) v[r] = cmul(x[(long long)r * P2 + j], twt[r * kLongColsPerCta + threadIdx.x]);
+    for (int r = 0; r < P1; ++r) v[r] = x[(long long)r * P2 + j];
+    col_twiddle<P1>(v, wbase);
     DftAny<P1, +1>::run(v);
     const int T = p.w.T;
     const int tj1 = 2 * pr, tj2 = 2 * pr + 1;

@@ -334,7 +334,7 @@ int fft_group(bool blue, int log2p) {
 constexpr size_t kLongRowSmem = (em::padded_len<em::kLongLog2P2>() + em::stage_tw_total(em::kLongLog2P2)) * sizeof(em::cplx);
 inline size_t long_col_smem(int p1) { return (size_t)p1 * em::kLongColsPerCta * sizeof(em::cplx); }
 constexpr int kLongColBlocks = em::kLongP2 / em::kLongColsPerCta;
-inline size_t long_pair_smem(int p1) { return ((size_t)p1 + (size_t)(p1 + 1) / 2 + 1) * 128 * sizeof(em::cplx); }
+inline size_t long_pair_smem(int p1) { return ((size_t)(p1 + 1) / 2 + 1) * 128 * sizeof(em::cplx); }
 
 int init_long_attrs() {
   CU_TRY(cudaFuncSetAttribute(em::em_long_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLongRowSmem));
@@ -438,8 +438,8 @@ int launch_long_colinv(proton_em_ctx* ctx, cudaStream_t st, int p1, bool blue, c
   switch (p1) {
 #define M(q)                                                                                              \
   case q:                                                                                                 \
-    if (blue) CU_TRY(launch_pdl(em::em_long_colinv_kernel<q, true>, grid, em::kLongColsPerCta, long_col_smem(q), st, cp)); \
-    else CU_TRY(launch_pdl(em::em_long_colinv_kernel<q, false>, grid, em::kLongColsPerCta, long_col_smem(q), st, cp));     \
+    if (blue) CU_TRY(launch_pdl(em::em_long_colinv_kernel<q, true>, grid, em::kLongColsPerCta, 0, st, cp)); \
+    else CU_TRY(launch_pdl(em::em_long_colinv_kernel<q, false>, grid, em::kLongColsPerCta, 0, st, cp));     \
     break;
     FOR_EACH_P1(M)
 #undef M
@@ -1033,7 +1033,8 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
       w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p;
       w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
       w.critical = critical;
-      const int tpc = std::max(1, cnt / 24);
+      static const int col_div = [] { const char* e = std::getenv("PROTON_EM_COL_DIV"); const int v = e ? std::atoi(e) : 0; return v > 0 ? v : 48; }();
+      const int tpc = std::max(1, cnt / col_div);
       const int groups = (cnt + tpc - 1) / tpc;
       em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
       em::RowParams rp{xbuf, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
