@@ -120,6 +120,29 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def bind_to_gpu_numa(index: int):
+    """Run this process on the CPUs of the GPU's NUMA node, so that pinned host buffers are allocated next to it
+    (the e2e leg is bound by host<->device copies).  Returns a description for `config`, or None if unknown."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(index)
+        dev = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(Path(f"/sys/bus/pci/devices/{dev}/numa_node").read_text().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in Path(f"/sys/devices/system/node/node{node}/cpulist").read_text().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return f"numa node {node} ({len(cpus)} cpus)"
+    except Exception:
+        return None
+
+
 def measured_peaks():
     p = REPO / "MEASURED_PEAKS.json"
     if p.exists():
@@ -246,6 +269,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    all_cpus = os.sched_getaffinity(0)
+    numa = bind_to_gpu_numa(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
@@ -434,6 +459,7 @@ def main():
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        os.sched_setaffinity(0, all_cpus)          # the CPU baseline gets every host core
         cpu_baseline = cpu_baseline_port(batch, ts)
 
     if rank == 0:
@@ -445,7 +471,7 @@ def main():
                            "max_nodes_per_line": int(batch.num_nodes.max()),
                            "l2": f"outputs of one step are {out_bytes / 2**30:.1f} GiB per GPU, far larger than the 126 MB L2",
                            "parallelism": f"lines sharded over {world} GPU(s), LPT segment-balanced",
-                           "imbalance_max_over_mean": desc.get("imbalance_max_over_mean")},
+                           "imbalance_max_over_mean": desc.get("imbalance_max_over_mean"), "host_affinity": numa},
                 "clocks": clocks, "gpu_launches": int(launches), "roofline": roofline, "e2e": e2e,
                 "cpu_baseline": cpu_baseline,
                 "pack_ms": {"first_call_with_table_build": pack_first_ms, "cached_tables": pack_ms}}
