@@ -1,5 +1,5 @@
 // em_long.cuh — long lines: transforms that do not fit one CTA's shared memory (P = P1 * 4096 complex
-// points, P1 in {4, 8, 16, 32}; Bluestein lines with 4096 < N <= 65536, power-of-two lines up to 131072).
+// points, P1 in {3..16, 18, 20, .., 32}; Bluestein lines with 4096 < N <= 65536, power-of-two lines up to 131072).
 //
 // Same mathematics as em_fft.cuh (two timestamps per complex transform, Makhoul permutation, Bluestein
 // with a DIF forward / DIT inverse pair so no reordering pass exists), factored as P = P1 x P2 with
@@ -10,7 +10,8 @@
 //   inverse  : column pass  u[j + q P2] = sum_r (X[r*P2 + j] w_P^{+jr}) w_P1^{+qr}
 // The passes exchange data through a scratch buffer in global memory that is sized to stay resident in
 // the 126 MB L2 (a wave of transforms at a time).  Kernels:
-//   em_long_colfwd_kernel     modal factors + pre-chirp + forward column pass (Bluestein) / chirp input (table build)
+//   em_long_colfwd_paired_kernel  modal factors + pre-chirp + forward column pass (Bluestein evaluation)
+//   em_long_colfwd_kernel     forward column pass over the chirp (table build, once per distinct N)
 //   em_long_scatter_kernel    power-of-two lines: modal factors, U_k written where the row DIT expects it
 //   em_long_row_kernel        row pass (forward * H * inverse, forward only, or inverse only)
 //   em_long_colinv_kernel     inverse column pass + post-chirp + de-interleave + stress store + partial max
@@ -125,28 +126,15 @@ struct LongWave {
   double critical;
 };
 
-// Packed spectrum entry Z_k (before the pre-twiddle) straight from lambda / W: the thread evaluates the modal factor
-// of mode k and of its mirror N-k for both timestamps (the mirror's owner does the same; the FP64 pipe has the slack,
-// a separate modal pass through global memory does not pay).
-__device__ __forceinline__ cplx long_zk(const double* __restrict__ lam, const double* __restrict__ W, int k, int N,
-                                        double w1, double t1, double w2, double t2) {
-  const double l = lam[k], wk = W[k];
-  const double y1 = em_modal(l, wk, w1, t1, nullptr), y2 = em_modal(l, wk, w2, t2, nullptr);
-  if (k == 0) return cplx{y1, y2};
-  const double lm = lam[N - k], wm = W[N - k];
-  const double m1 = em_modal(lm, wm, w1, t1, nullptr), m2 = em_modal(lm, wm, w2, t2, nullptr);
-  return cplx{y1 + m2, y2 - m1};
-}
-
-// ---- forward column pass (Bluestein) ----------------------------------------------------------------
-// mode 0: x = pre-chirped spectrum of the wave's transforms;  mode 1: x = conj chirp / P (table build,
-// one "transform" per entry of `tabs_build`).
+// ---- forward column pass ---------------------------------------------------------------------------------
+// Parameters shared by the column kernels.  `mode` / `tabs_build` are used by the table build only
+// (em_long_colfwd_kernel: x = conj chirp / P, one "transform" per entry of `tabs_build`).
 struct ColParams {
   LongWave w;
   int mode;
   const NTab* tabs_build;
   int tr_per_cta;
-  const cplx* twl;       // [P1][P2]  w_P^{+j r}  (em_long_twiddle_kernel)
+  const cplx* twl;       // [P1][P2]  w_P^{+j r}  (em_long_twiddle_kernel); the evaluation kernels read row r = 1 only
 };
 
 __global__ void __launch_bounds__(256) em_long_twiddle_kernel(cplx* twl, int P1) {
@@ -174,6 +162,7 @@ __global__ void __launch_bounds__(256) em_long_prepost_kernel(const NTab* tabs_b
   }
 }
 
+// Table build: forward column pass over the conjugate chirp of each new length (run once per distinct N).
 template <int P1>
 __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const ColParams p) {
   constexpr int P2 = kLongP2;
@@ -189,40 +178,19 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const C
   const int s1 = min(p.w.n_tr, s0 + p.tr_per_cta);
   for (int s = s0; s < s1; ++s) {
     cplx v[P1];
-    int N;
-    if (p.mode == 0) {
-      const int line = p.w.tr_line[s], pr = p.w.tr_pair[s];
-      N = p.w.num_nodes[line];
-      const NTab tab = p.w.tabs[p.w.line_tab[line]];
-      const double* W = p.w.W + p.w.node_off[line];
-      const double a = p.w.a_coeff[line];
-      const double t1 = p.w.ts[2 * pr];
-      const double t2 = (2 * pr + 1 < p.w.T) ? p.w.ts[2 * pr + 1] : t1;
-      const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
+    const NTab tab = p.tabs_build[s];
+    const int N = tab.n;
+    const double inv_p = 1.0 / (double)P;
 #pragma unroll
-      for (int q = 0; q < P1; ++q) {
-        const int k = j + q * P2;
-        v[q] = cplx{0.0, 0.0};
-        if (q < (P1 + 1) / 2 + 1 && k < N) {    // Bluestein: 2N-1 <= P, rows above P1/2 are zero
-          const cplx z = long_zk(tab.lam, W, k, N, w1, t1, w2, t2);
-          v[q] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
-        }
-      }
-    } else {
-      const NTab tab = p.tabs_build[s];
-      N = tab.n;
-      const double inv_p = 1.0 / (double)P;
-#pragma unroll
-      for (int q = 0; q < P1; ++q) {
-        const long long i = j + (long long)q * P2;
-        long long d = -1;
-        if (i < N) d = i; else if (P - i < N) d = P - i;
-        v[q] = cplx{0.0, 0.0};
-        if (d >= 0) {
-          const unsigned long long dd = (unsigned long long)d;
-          const cplx c = em_cis_frac((dd * dd) % (2ULL * N), (unsigned long long)N);
-          v[q] = cplx{c.x * inv_p, -c.y * inv_p};
-        }
+    for (int q = 0; q < P1; ++q) {
+      const long long i = j + (long long)q * P2;
+      long long d = -1;
+      if (i < N) d = i; else if (P - i < N) d = P - i;
+      v[q] = cplx{0.0, 0.0};
+      if (d >= 0) {
+        const unsigned long long dd = (unsigned long long)d;
+        const cplx c = em_cis_frac((dd * dd) % (2ULL * N), (unsigned long long)N);
+        v[q] = cplx{c.x * inv_p, -c.y * inv_p};
       }
     }
     DftAny<P1, -1>::run(v);
@@ -233,7 +201,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colfwd_kernel(const C
   }
 }
 
-// Forward column pass for the evaluation (mode 0) with every modal factor evaluated ONCE: entry k of the packed
+// Forward column pass of the evaluation with every modal factor evaluated ONCE: entry k of the packed
 // spectrum needs the modal values of k and of its mirror N-k, which lives in column (N mod 4096) - j.  A CTA therefore
 // owns 64 column PAIRS {j, mirror(j)} (threads 0..63 one side, 64..127 the other), each thread evaluates only its own
 // modes and the two sides swap through shared memory.  Slot a pairs columns c/2 + a and c/2 - a (c = N mod 4096; for

@@ -1,10 +1,15 @@
 // proton_em.cu — host side of libproton_em.so: the C ABI declared in include/proton_em.h.
 //
-// Owns the context (stream, constant tables, per-length table cache), the plan (a packed ragged batch
+// Owns the context (streams, constant tables, per-length table cache), the plan (a packed ragged batch
 // resident in HBM) and the launch logic that routes each line to a kernel by its length:
-//   N <= 32                      em_eval_small_kernel   (cosine table, one warp per line)
-//   N = 2^p, 64..8192            em_eval_fft_kernel<p, false>   (in-CTA radix-8 DIT FFT)
+//   N <= 88 (not 64)             em_eval_dense_kernel<MT>       (DMMA contraction with the N x N cosine matrix)
+//   N = 2^p, 64..8192            em_eval_fft_kernel<p, false>   (in-CTA DIT FFT, radix 16/8/4/2)
 //   other N <= 4096              em_eval_fft_kernel<p, true>    (Bluestein, P = 2^p >= 2N-1)
+//   other N <= 65536, 2^p <= 131072   em_long_{colfwd_paired | scatter} -> em_long_row -> em_long_colinv
+//                                (P = P1 x 4096 through an L2-resident scratch, waves dealt to `lanes` streams)
+// Tuning knobs, all optional environment variables read once: PROTON_EM_LANES (2), PROTON_EM_LONG_WAVE_MB (32),
+// PROTON_EM_PDL (1), PROTON_EM_COL_DIV (48), PROTON_EM_DENSE_MAX (88), PROTON_EM_CHUNK_MB (256),
+// PROTON_EM_SMALL=table, PROTON_EM_TRACE.
 // There is no CPU fallback: every entry point fails with PROTON_EM_ECUDA when no device is usable.
 #include "../../include/proton_em.h"
 
@@ -352,9 +357,7 @@ int init_long_attrs() {
   CU_TRY(cudaFuncSetAttribute(em::em_long_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLongRowSmem));
 #define M(q)                                                                                                              \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));        \
-  CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_paired_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_pair_smem(q))); \
-  CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));  \
-  CU_TRY(cudaFuncSetAttribute(em::em_long_colinv_kernel<q, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));
+  CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_paired_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_pair_smem(q)));
   FOR_EACH_P1(M)
 #undef M
   // twiddles of the non-power-of-two column DFTs
