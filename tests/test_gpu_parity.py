@@ -128,8 +128,8 @@ def test_random_ragged_batch_against_oracle(ctx, oracle):
 def test_long_lines_against_oracle(ctx, oracle, T):
     """Lines whose transform does not fit one CTA (multi-pass path with L2-resident scratch)."""
     rng = np.random.default_rng(900 + T)
-    sizes = [4097, 5000, 8191, 8193, 12000, 16384, 16385, 17000, 20670, 22000, 26000, 30000, 32768, 40000, 65536, 65000,
-             100, 64]
+    sizes = [4097, 5000, 8191, 8193, 12000, 16384, 16385, 17000, 20670, 22000, 26000, 30000, 32768, 40000, 50000, 57000,
+             61000, 65536, 65000, 100, 64]
     batch = synth_batch(rng, sizes)
     ts = np.array([1e6, 2e7, 6.38e8, 1e8])[:T]
     got = ctx.analyze_host(batch, ts, critical=40e6)
