@@ -32,8 +32,8 @@ constexpr int kLongRowThreads = plan16(kLongLog2P2) ? 256 : 512;     // one butt
 constexpr int kLongMaxP1 = 32;
 __constant__ cplx kDftTw[kLongMaxP1 + 1][kLongMaxP1];
 
-// Column DFT of any length R <= 32: radix-2 recursion for powers of two, the plain O(R^2) sum otherwise (the column
-// kernels wait on memory, not on the FP64 pipe).
+// Column DFT of any length R <= 32: radix-2 recursion for powers of two and even lengths, the symmetric O(R^2 / 4)
+// form for odd lengths.
 template <int R, int SIGN> struct DftAny {
   static __device__ __forceinline__ void run(cplx (&v)[R]) {
     if constexpr ((R & (R - 1)) == 0) {
@@ -57,22 +57,32 @@ template <int R, int SIGN> struct DftAny {
         v[r + R / 2] = csub(e[r], t);
       }
     } else {
+      // odd length: pair q with R-q.  e^{i t} v_q + e^{-i t} v_{R-q} = cos t (v_q + v_{R-q}) + i sin t (v_q - v_{R-q}), so
+      // outputs r and R-r share A_r = sum_q cos(2 pi q r / R) s_q and B_r = sum_q sin(2 pi q r / R) d_q: (R-1)^2 real
+      // FMAs instead of 4 R (R-1).
+      constexpr int H = (R - 1) / 2;
+      cplx sm[H + 1], df[H + 1];
+      cplx y0 = v[0];
+#pragma unroll
+      for (int q = 1; q <= H; ++q) {
+        sm[q] = cadd(v[q], v[R - q]);
+        df[q] = csub(v[q], v[R - q]);
+        y0 = cadd(y0, sm[q]);
+      }
       cplx y[R];
+      y[0] = y0;
 #pragma unroll
-      for (int r = 0; r < R; ++r) {
-        cplx acc = v[0];
+      for (int r = 1; r <= H; ++r) {
+        cplx A = v[0], B = cplx{0.0, 0.0};
 #pragma unroll
-        for (int q = 1; q < R; ++q) {
-          const int m = (q * r) % R;
-          if (m == 0) acc = cadd(acc, v[q]);
-          else {
-            const cplx w = kDftTw[R][m];
-            const double wy = SIGN > 0 ? w.y : -w.y;
-            acc.x = fma(v[q].x, w.x, fma(-v[q].y, wy, acc.x));
-            acc.y = fma(v[q].x, wy, fma(v[q].y, w.x, acc.y));
-          }
+        for (int q = 1; q <= H; ++q) {
+          const cplx w = kDftTw[R][(q * r) % R];          // (cos, sin) of 2 pi q r / R
+          A.x = fma(w.x, sm[q].x, A.x); A.y = fma(w.x, sm[q].y, A.y);
+          B.x = fma(w.y, df[q].x, B.x); B.y = fma(w.y, df[q].y, B.y);
         }
-        y[r] = acc;
+        constexpr double sg = (double)SIGN;
+        y[r] = cplx{A.x - sg * B.y, A.y + sg * B.x};
+        y[R - r] = cplx{A.x + sg * B.y, A.y - sg * B.x};
       }
 #pragma unroll
       for (int r = 0; r < R; ++r) v[r] = y[r];

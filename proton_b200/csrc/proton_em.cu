@@ -79,9 +79,10 @@ constexpr int kMaxBlueN = (1 << (kMaxLog2P - 1));  // 4096: 2N-1 <= 8192
 // Long lines: P = P1 * 4096 with P1 from this list (any P1 works for Bluestein; powers of two for 2^p lines).
 constexpr int kLongP1List[] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 18, 20, 22, 24, 26, 28, 30, 32};
 // Measured Gevals/s of a full transform per row count (B200, T = 100, tools/profile_step.py --uniform 2048*P1-10):
-// odd and large row counts cost more in the column passes, so e.g. 16 rows beat 15 and 32 beat 26..30.
-constexpr double kLongP1Gevals[] = {52.3, 52.9, 52.3, 51.9, 51.1, 52.2, 47.5, 49.8, 45.6, 49.5, 43.6, 45.2, 38.2, 48.3,
-                                    40.4, 40.8, 33.3, 35.0, 30.9, 32.8, 29.0, 38.3};
+// odd and large row counts cost more in the column passes, so e.g. 16 rows beat 15 and 32 beat 28 and 30
+// (PROTON_EM_P1_SMALLEST=1 forces the smallest fitting count, for re-measuring this table).
+constexpr double kLongP1Gevals[] = {52.5, 53.0, 52.8, 52.2, 51.7, 52.0, 50.2, 51.5, 47.1, 50.0, 45.7, 45.8, 40.5, 48.4,
+                                    43.8, 40.8, 35.5, 35.2, 34.1, 33.9, 32.1, 37.7};
 static_assert(sizeof(kLongP1Gevals) / sizeof(double) == sizeof(kLongP1List) / sizeof(int), "one figure per row count");
 constexpr int kMaxLongPow2N = em::kLongP2 * em::kLongMaxP1;                 // 131072
 constexpr int kMaxLongBlueN = (em::kLongP2 * em::kLongMaxP1) / 2;           // 65536: 2N-1 <= 131072
@@ -120,7 +121,8 @@ ClassOf classify(int N) {
     for (size_t i = 0; i < sizeof(kLongP1List) / sizeof(kLongP1List[0]); ++i) {
       const int p1 = kLongP1List[i];
       if ((long long)p1 * em::kLongP2 < need) continue;
-      const double cost = (double)p1 / kLongP1Gevals[i];
+      static const bool smallest = [] { const char* e = std::getenv("PROTON_EM_P1_SMALLEST"); return e && std::atoi(e) != 0; }();
+      const double cost = smallest ? (double)p1 : (double)p1 / kLongP1Gevals[i];   // (override: for re-measuring the table)
       if (!best || cost < best_cost) { best = p1; best_cost = cost; }
     }
     return best ? ClassOf{CLS_LBLUE, best} : ClassOf{CLS_NONE, 0};
