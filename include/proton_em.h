@@ -105,6 +105,19 @@ int proton_em_synchronize(proton_em_ctx* ctx);
 void* proton_em_stream(proton_em_ctx* ctx);
 /* Number of kernel launches issued by this ctx so far (bench.py reports it as gpu_launches). */
 int64_t proton_em_launch_count(const proton_em_ctx* ctx);
+/* Piecewise-constant current history (restart in time).  No counterpart in the reference, whose
+ * kernel starts from zero stress and carries one constant current (bin/EMtool_analytical@0xc68c has no sigma_0 input).
+ * Segment s applies the current densities curden_seg[s] (laid out like batch->curden; batch->curden itself is ignored)
+ * from seg_start[s] on; seg_start[0] must be 0 and the times must increase.  The stress equation is linear, so
+ *     sigma(t) = sum over s with seg_start[s] < t of  sigma_ref[curden_seg[s] - curden_seg[s-1]](t - seg_start[s]),
+ * every term being the reference's closed form for a current increment switched on at seg_start[s] (the modal state
+ * never leaves the DCT basis, so no forward transform of a stress field is needed).  Each increment is evaluated with
+ * the kernels of proton_em_eval into a second field, added to the total, and max / argmax / flag are taken from the
+ * total.  All pointers are host pointers; `result` as in proton_em_analyze_host (stress may be NULL). */
+int proton_em_analyze_history_host(proton_em_ctx* ctx, const proton_em_batch* batch, const double* const* curden_seg,
+                                   const double* seg_start, int32_t num_segments, const double* ts, int32_t T,
+                                   const proton_em_opts* opts, const proton_em_result* result);
+
 /* Per-kernel timing for bench.py's roofline (no counterpart in the reference).  While enabled, every launch of
  * the evaluation path is bracketed by a CUDA event pair on the stream it is launched on; the call synchronises
  * the device, folds the finished pairs into per-kind totals, and (enable != 0 after being off) clears them.

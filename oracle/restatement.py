@@ -140,6 +140,32 @@ def batch(num_nodes, a_coeff, trip_off, rows, cols, vals, u_off, u, ts, want_str
     return stress, mx, amx
 
 
+def history_batch(num_nodes, a_coeff, trip_off, rows, cols, vals, u_off, curden_segments, seg_start, ts,
+                  use_double=False):
+    """Piecewise-constant current history (product: proton_em_analyze_history_host; no counterpart in the reference).
+    Superposition of the reference closed form over the current increments, each started at its switching time:
+    sigma(t) = sum_s sigma_ref[u_s - u_{s-1}](max(t - tau_s, 0)).  Independently pinned by tests/test_history.py
+    against a stiff ODE integration of d sigma/dt = a L sigma + B u(t).  -> (stress, max[L,T], argmax[L,T])"""
+    ts = np.ascontiguousarray(np.atleast_1d(ts), dtype=np.float64)
+    num_nodes = np.ascontiguousarray(num_nodes, dtype=np.int32)
+    total = None
+    prev = None
+    for u, tau in zip(curden_segments, seg_start):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        incr = u if prev is None else u - prev
+        prev = u
+        st, _, _ = batch(num_nodes, a_coeff, trip_off, rows, cols, vals, u_off, incr, np.maximum(ts - tau, 0.0),
+                         use_double=use_double)
+        total = st if total is None else total + st
+    L, T = len(num_nodes), len(ts)
+    off = np.concatenate([[0], np.cumsum(num_nodes.astype(np.int64))])
+    mx = np.empty((L, T)); amx = np.empty((L, T), np.int32)
+    for l in range(L):
+        blk = total[off[l] * T:off[l + 1] * T].reshape(T, int(num_nodes[l]))
+        mx[l] = blk.max(axis=1); amx[l] = blk.argmax(axis=1)
+    return total, mx, amx
+
+
 def max_threads() -> int:
     return int(load().em_oracle_max_threads())
 

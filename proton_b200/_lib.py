@@ -46,7 +46,8 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_plan_destroy", "proton_em_plan_total_nodes", "proton_em_plan_num_lines",
            "proton_em_plan_scratch_bytes", "proton_em_eval", "proton_em_synchronize", "proton_em_stream",
            "proton_em_launch_count", "proton_em_analyze_host", "proton_em_run_cfg", "proton_em_debug_exp",
-           "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read"]
+           "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read",
+           "proton_em_analyze_history_host"]
 
 
 def load() -> ctypes.CDLL:
@@ -79,6 +80,8 @@ def load() -> ctypes.CDLL:
     lib.proton_em_debug_expm1.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_eval_line_noalloc.argtypes = [ctypes.c_int, vp, ctypes.c_int32, ctypes.c_double, ctypes.c_int32, vp, vp,
                                                 vp, ctypes.c_int32, vp, vp, ctypes.c_int32, ctypes.c_double, vp, vp, vp, vp]
+    lib.proton_em_analyze_history_host.argtypes = [vp, ctypes.POINTER(Batch), ctypes.POINTER(vp), vp, ctypes.c_int32, vp,
+                                                   ctypes.c_int32, ctypes.POINTER(Opts), ctypes.POINTER(Result)]
     lib.proton_em_profile.argtypes = [vp, ctypes.c_int]
     lib.proton_em_profile_read.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
                                            ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]

@@ -192,6 +192,30 @@ class Context:
                                                ctypes.byref(res), int(max_device_bytes)))
         return out
 
+    def analyze_history(self, batch: LineBatch, curden_segments, seg_start, ts, critical=None, want_stress=True,
+                        algorithm=ALG_AUTO) -> EvalResult:
+        """Stress under a piecewise-constant current history: segment s applies `curden_segments[s]` (each laid out
+        like `batch.curden`) from `seg_start[s]` on (seg_start[0] == 0).  See proton_em_analyze_history_host."""
+        ts = np.ascontiguousarray(np.atleast_1d(ts), dtype=np.float64)
+        seg_start = np.ascontiguousarray(np.atleast_1d(seg_start), dtype=np.float64)
+        segs = [np.ascontiguousarray(c, dtype=np.float64) for c in curden_segments]
+        if len(segs) != len(seg_start):
+            raise ValueError("one start time per current segment")
+        for c in segs:
+            if c.shape != np.asarray(batch.curden).shape:
+                raise ValueError("every segment needs one current density per entry of batch.curden")
+        T, L = len(ts), batch.num_lines
+        out = EvalResult(np.empty(batch.total_nodes * T) if want_stress else None, np.empty((L, T)),
+                         np.empty((L, T), np.int32), np.empty((L, T), np.uint8), batch.node_off, T)
+        res = Result(out.stress.ctypes.data if out.stress is not None else None, out.max_stress.ctypes.data,
+                     out.argmax.ctypes.data, out.flag.ctypes.data)
+        ptrs = (ctypes.c_void_p * len(segs))(*[c.ctypes.data for c in segs])
+        cb = batch._as_c()
+        o = _opts(critical, algorithm)
+        check(self._lib.proton_em_analyze_history_host(self._h, ctypes.byref(cb), ptrs, seg_start.ctypes.data, len(segs),
+                                                       ts.ctypes.data, T, ctypes.byref(o), ctypes.byref(res)))
+        return out
+
     def debug_exp(self, x) -> np.ndarray:
         x = np.ascontiguousarray(x, dtype=np.float64)
         y = np.empty_like(x)

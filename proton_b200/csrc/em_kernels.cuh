@@ -506,4 +506,57 @@ __global__ void __launch_bounds__(128) em_eval_dense_kernel(const SmallParams p)
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Current histories (proton_em_analyze_history_host): the stress of a piecewise-constant current is the sum of the
+// reference solutions of the current increments, each started at its switching time.  The increments are evaluated
+// by the kernels above into a second field; these two kernels add it to the running total and take the per-(line, t)
+// reductions of the total.  Both are plain HBM streams (24 and 8 bytes per eval).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) em_accumulate_kernel(double* __restrict__ total, const double* __restrict__ add,
+                                                            long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) total[i] += add[i];
+}
+
+struct RowMaxParams {
+  const double* stress;        // indexed by global node offset (node_off[line] * T + t * N)
+  const long long* node_off;
+  const int* num_nodes;
+  long long line0;             // first line of this launch
+  int T;
+  double* mx; int* amx; unsigned char* flag;
+  double critical;
+};
+
+__global__ void __launch_bounds__(128) em_rowmax_kernel(const RowMaxParams p) {
+  const long long row = blockIdx.x;
+  const long long line = p.line0 + row / p.T;
+  const int tj = (int)(row % p.T);
+  const int N = p.num_nodes[line];
+  const double* src = p.stress + p.node_off[line] * (long long)p.T + (long long)tj * N;
+  double best = -__longlong_as_double(0x7ff0000000000000LL);
+  int besti = 0x7fffffff;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    const double v = src[n];
+    if (v > best) { best = v; besti = n; }
+  }
+  __shared__ double sv[4];
+  __shared__ int si[4];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+    if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = besti; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int q = 1; q < 4; ++q)
+      if (sv[q] > best || (sv[q] == best && si[q] < besti)) { best = sv[q]; besti = si[q]; }
+    if (besti == 0x7fffffff) { besti = 0; best = src[0]; }       // all NaN: report the first value like the fused kernels
+    const long long o = line * p.T + tj;
+    p.mx[o] = best; p.amx[o] = besti; p.flag[o] = (best > p.critical) ? 1 : 0;
+  }
+}
+
 }  // namespace em

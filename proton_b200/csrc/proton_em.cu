@@ -21,6 +21,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <limits>
 #include <sstream>
 #include <string>
 #include <thread>
@@ -203,7 +204,7 @@ struct proton_em_ctx {
   // host-buffer path (proton_em_analyze_host): cached device staging, a copy stream, per-buffer events
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_done[2] = {}, ev_copied[2] = {};
-  DevBuf<double> io_stress[2], io_mx, io_ts;
+  DevBuf<double> io_stress[2], io_mx, io_ts, io_tmp;
   DevBuf<int> io_amx;
   DevBuf<unsigned char> io_flag;
   DevBuf<em::cplx> long_x, long_y;
@@ -732,7 +733,7 @@ int proton_em_destroy(proton_em_ctx* ctx) {
     if (ctx->ev_copied[i]) cudaEventDestroy(ctx->ev_copied[i]);
     ctx->io_stress[i].free();
   }
-  ctx->io_mx.free(); ctx->io_ts.free(); ctx->io_amx.free(); ctx->io_flag.free();
+  ctx->io_mx.free(); ctx->io_ts.free(); ctx->io_amx.free(); ctx->io_flag.free(); ctx->io_tmp.free();
   if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
   if (ctx->d_exp) cudaFree(ctx->d_exp);
   for (auto* p : ctx->d_tw) if (p) cudaFree(p);
@@ -1288,6 +1289,105 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const d
   tr.lap("main stream done");
   CU_TRY(cudaStreamSynchronize(cs));
   tr.lap("copy stream done");
+  return PROTON_EM_OK;
+}
+
+int proton_em_analyze_history_host(proton_em_ctx* ctx, const proton_em_batch* b, const double* const* curden_seg,
+                                   const double* seg_start, int32_t num_segments, const double* ts, int32_t T,
+                                   const proton_em_opts* opts, const proton_em_result* res) {
+  if (!ctx || !b || !res || !curden_seg || !seg_start)
+    return fail(PROTON_EM_EINVAL, "proton_em_analyze_history_host: NULL argument");
+  if (num_segments <= 0) return fail(PROTON_EM_EINVAL, "proton_em_analyze_history_host: need at least one segment");
+  if (T <= 0 || b->num_lines <= 0) return PROTON_EM_OK;
+  if (!ts || !res->max_stress || !res->argmax || !res->flag)
+    return fail(PROTON_EM_EINVAL, "proton_em_analyze_history_host: ts, max_stress, argmax and flag are required");
+  if (seg_start[0] != 0.0) return fail(PROTON_EM_EINVAL, "the first segment must start at t = 0 (got %g)", seg_start[0]);
+  for (int s = 1; s < num_segments; ++s)
+    if (!(seg_start[s] > seg_start[s - 1]))
+      return fail(PROTON_EM_EINVAL, "segment start times must increase (segment %d: %g after %g)", s, seg_start[s], seg_start[s - 1]);
+  for (int s = 0; s < num_segments; ++s)
+    if (!curden_seg[s]) return fail(PROTON_EM_EINVAL, "curden_seg[%d] is NULL", s);
+  { int rc = set_device(ctx); if (rc) return rc; }
+  const int64_t L = b->num_lines;
+  if (!b->u_off) return fail(PROTON_EM_EINVAL, "batch.u_off is NULL");
+  const int64_t nu = b->u_off[L];
+  static const int64_t chunk_mb = [] { const char* e = std::getenv("PROTON_EM_CHUNK_MB"); const long long v = e ? std::atoll(e) : 0; return (int64_t)(v > 0 ? v : 256); }();
+  const int64_t chunk_nodes = std::max<int64_t>(1, (chunk_mb << 20) / (8 * (int64_t)T));
+  // one plan per segment, packed from the current INCREMENT of that segment
+  std::vector<proton_em_plan*> plans;
+  struct PG { std::vector<proton_em_plan*>& v; ~PG() { for (proton_em_plan* p : v) destroy_plan(p); } } pg{plans};
+  std::vector<double> incr((size_t)nu);
+  std::vector<int> live;                       // segments that start before the last timestamp
+  double t_last = ts[0];
+  for (int j = 1; j < T; ++j) t_last = std::max(t_last, ts[j]);
+  for (int s = 0; s < num_segments; ++s) {
+    if (s > 0 && !(seg_start[s] < t_last)) break;
+    for (int64_t i = 0; i < nu; ++i) incr[(size_t)i] = curden_seg[s][i] - (s ? curden_seg[s - 1][i] : 0.0);
+    proton_em_batch bs = *b;
+    bs.curden = incr.data();
+    proton_em_plan* plan = nullptr;
+    int rc = pack_impl(ctx, &bs, PROTON_EM_HOST, chunk_nodes, &plan);     // copies the increment to the device
+    if (rc) return rc;
+    plans.push_back(plan);
+    live.push_back(s);
+  }
+  const int S = (int)plans.size();
+  proton_em_plan* p0 = plans[0];
+  const size_t LT = (size_t)L * T;
+  int64_t max_nodes = 0;
+  for (const auto& ch : p0->chunks) max_nodes = std::max<int64_t>(max_nodes, p0->node_off[ch.l1] - p0->node_off[ch.l0]);
+  const size_t field = (size_t)max_nodes * T;
+  CU_TRY(cudaDeviceSynchronize());
+  CU_TRY(grow(ctx->io_ts, (size_t)T * S)); CU_TRY(grow(ctx->io_mx, LT)); CU_TRY(grow(ctx->io_amx, LT)); CU_TRY(grow(ctx->io_flag, LT));
+  CU_TRY(grow(ctx->io_stress[0], field)); CU_TRY(grow(ctx->io_stress[1], field)); CU_TRY(grow(ctx->io_tmp, field));
+  cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
+  // timestamps of segment s: time since its start, clipped at 0 (the reference solution is 0 at t = 0)
+  std::vector<double> tsh((size_t)T * S);
+  for (int k = 0; k < S; ++k)
+    for (int j = 0; j < T; ++j) tsh[(size_t)k * T + j] = std::max(0.0, ts[j] - seg_start[live[k]]);
+  CU_TRY(cudaMemcpyAsync(ctx->io_ts.p, tsh.data(), tsh.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  const double critical = opts ? opts->critical_stress : NAN;          // as in proton_em_eval: NaN never flags
+  for (int c = 0; c < (int)p0->chunks.size(); ++c) {
+    const auto& ch = p0->chunks[c];
+    const int bi = c & 1;
+    const int64_t n0 = p0->node_off[ch.l0], n1 = p0->node_off[ch.l1];
+    const long long count = (long long)(n1 - n0) * T;
+    if (c >= 2 && res->stress) CU_TRY(cudaStreamWaitEvent(st, ctx->ev_copied[bi], 0));
+    double* d_total = ctx->io_stress[bi].p - n0 * (int64_t)T;             // kernels index by global node offset
+    double* d_tmp = ctx->io_tmp.p - n0 * (int64_t)T;
+    for (int k = 0; k < S; ++k) {
+      int rc = eval_device(plans[k], ctx->io_ts.p + (size_t)k * T, T, opts, k == 0 ? d_total : d_tmp, ctx->io_mx.p,
+                           ctx->io_amx.p, ctx->io_flag.p, c, c + 1);
+      if (rc) { cudaDeviceSynchronize(); return rc; }
+      if (k > 0) {
+        const unsigned blocks = (unsigned)std::min<long long>((count + 255) / 256, (long long)ctx->sm_count * 16);
+        em::em_accumulate_kernel<<<blocks, 256, 0, st>>>(ctx->io_stress[bi].p, ctx->io_tmp.p, count);
+        ctx->launches++;
+        CU_TRY(cudaGetLastError());
+      }
+    }
+    if (S > 1) {   // the fused reductions of the last evaluation describe one increment only: redo them on the total
+      const long long rows = (long long)(ch.l1 - ch.l0) * T;
+      if (rows > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "chunk has too many (line, timestamp) rows");
+      em::RowMaxParams rp{d_total, p0->d_node_off.p, p0->d_num_nodes, (long long)ch.l0, T, ctx->io_mx.p, ctx->io_amx.p,
+                          ctx->io_flag.p, critical};
+      em::em_rowmax_kernel<<<(unsigned)rows, 128, 0, st>>>(rp);
+      ctx->launches++;
+      CU_TRY(cudaGetLastError());
+    }
+    if (res->stress) {
+      CU_TRY(cudaEventRecord(ctx->ev_done[bi], st));
+      CU_TRY(cudaStreamWaitEvent(cs, ctx->ev_done[bi], 0));
+      CU_TRY(cudaMemcpyAsync(res->stress + n0 * (int64_t)T, ctx->io_stress[bi].p, (size_t)count * sizeof(double),
+                             cudaMemcpyDeviceToHost, cs));
+      CU_TRY(cudaEventRecord(ctx->ev_copied[bi], cs));
+    }
+  }
+  CU_TRY(cudaMemcpyAsync(res->max_stress, ctx->io_mx.p, LT * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaMemcpyAsync(res->argmax, ctx->io_amx.p, LT * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaMemcpyAsync(res->flag, ctx->io_flag.p, LT * sizeof(unsigned char), cudaMemcpyDeviceToHost, st));
+  CU_TRY(cudaStreamSynchronize(st));
+  CU_TRY(cudaStreamSynchronize(cs));
   return PROTON_EM_OK;
 }
 

@@ -224,6 +224,36 @@ def test_per_kernel_profile_counts_the_launches(ctx):
     plan.close()
 
 
+def test_current_history_against_oracle_superposition(ctx, oracle):
+    """proton_em_analyze_history_host: piecewise-constant currents = sum of the reference solutions of the increments."""
+    from proton_b200.api import ProtonEmError
+    rng = np.random.default_rng(21)
+    batch = synth_batch(rng, [1, 5, 40, 64, 300, 1000, 3000, 5000, 9000])
+    base = np.asarray(batch.curden)
+    segs = [base, np.float32(rng.normal(0, 1e11, base.shape)).astype(np.float64), 0.25 * base, np.zeros_like(base)]
+    seg_start = np.array([0.0, 2.0e7, 2.0e8, 5.0e9])          # the last segment starts after every timestamp
+    ts = np.array([1e6, 2.0e7, 2.5e7, 1.9e8, 3.0e8, 6.38e8])
+    got = ctx.analyze_history(batch, segs, seg_start, ts, critical=40e6)
+    ws, wm, wa = oracle.history_batch(batch.num_nodes, batch.a_coeff, batch.trip_off, batch.trip_row, batch.trip_col,
+                                      batch.trip_val, batch.u_off, segs, seg_start, ts)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    self_consistent(batch, ts, got, 40e6)
+    print(f"history: worst norm-wise error {worst:.3e}")
+    # one segment is exactly the plain evaluation; repeating the same current changes nothing
+    one = ctx.analyze_history(batch, [base], [0.0], ts, critical=40e6)
+    plain = ctx.analyze_host(batch, ts, critical=40e6)
+    assert np.array_equal(one.stress, plain.stress) and np.array_equal(one.argmax, plain.argmax)
+    same = ctx.analyze_history(batch, [base, base, base], [0.0, 1e7, 3e8], ts, critical=40e6)
+    assert np.array_equal(same.stress, plain.stress) and np.array_equal(same.flag, plain.flag)
+    # reduce-only mode returns the reductions of the total
+    red = ctx.analyze_history(batch, segs, seg_start, ts, critical=40e6, want_stress=False)
+    assert red.stress is None and np.array_equal(red.max_stress, got.max_stress) and np.array_equal(red.argmax, got.argmax)
+    with pytest.raises(ProtonEmError, match="start at t = 0"):
+        ctx.analyze_history(batch, [base], [1.0], ts)
+    with pytest.raises(ProtonEmError, match="increase"):
+        ctx.analyze_history(batch, [base, base], [0.0, 0.0], ts)
+
+
 def test_errors_are_reported_not_swallowed(ctx):
     from proton_b200.api import LineBatch, ProtonEmError
     rng = np.random.default_rng(5)
