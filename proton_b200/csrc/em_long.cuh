@@ -416,9 +416,20 @@ __global__ void __launch_bounds__(kLongRowThreads, 2) em_long_row_kernel(const R
     stage_barrier<LOG2P, NST - 2>();
     DitStages<LOG2P, NST - 2, 1, NT>::run(data, 1, twb, tid);
   } else {
-    for (int i = tid; i < P2; i += NT) data[pad_idx<LOG2P>(i)] = row[i];
-    __syncthreads();
-    DitStages<LOG2P, NST - 1, 1, NT>::run(data, 1, twb, tid);
+    // power-of-two lines: the innermost DIT stage (stride 1, no twiddles) takes its consecutive inputs straight
+    // from the row
+    constexpr int RM = stage_radix<LOG2P, NST - 1>();
+    for (int b = tid; b < P2 / RM; b += NT) {
+      cplx v[RM];
+#pragma unroll
+      for (int q = 0; q < RM; ++q) v[q] = row[b * RM + q];
+      Dft<RM, +1>::run(v);
+      cplx* d = data + pad_idx<LOG2P>(b * RM);
+#pragma unroll
+      for (int q = 0; q < RM; ++q) d[q] = v[q];
+    }
+    stage_barrier<LOG2P, NST - 2>();
+    DitStages<LOG2P, NST - 2, 1, NT>::run(data, 1, twb, tid);
   }
   row_dit_to_global<NT>(row, data, twb, tid);
 }
