@@ -164,18 +164,34 @@ struct Arena {
   }
 };
 
+// Device buffers of plans and of the host-buffer paths come from a per-context CUDA memory pool, stream-ordered on
+// the context's main stream (every other stream the library uses forks from and joins into it): repeated
+// proton_em_analyze_host calls then cost microseconds instead of ~4 ms of cudaMalloc / cudaFree per call.  The entry
+// points name the pool and stream of their context here (set_device); PROTON_EM_ASYNC_ALLOC=0 falls back to cudaMalloc.
+thread_local cudaMemPool_t tl_pool = nullptr;
+thread_local cudaStream_t tl_stream = nullptr;
+
 template <typename T>
 struct DevBuf {
   T* p = nullptr;
   size_t n = 0;
+  bool pooled = false;
   cudaError_t alloc(size_t count) {
     free();
     n = count;
     if (count == 0) return cudaSuccess;
+    if (tl_pool) {
+      pooled = true;
+      return cudaMallocFromPoolAsync(reinterpret_cast<void**>(&p), count * sizeof(T), tl_pool, tl_stream);
+    }
+    pooled = false;
     return cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T));
   }
   void free() {
-    if (p) cudaFree(p);
+    if (p) {
+      if (pooled && tl_pool) cudaFreeAsync(p, tl_stream);
+      else cudaFree(p);
+    }
     p = nullptr;
     n = 0;
   }
@@ -188,6 +204,7 @@ struct proton_em_ctx {
   int device = 0;
   int sm_count = 148;
   cudaStream_t stream = nullptr;
+  cudaMemPool_t pool = nullptr;             // stream-ordered pool behind every DevBuf of this context (may be null)
   ulonglong2* d_exp = nullptr;
   em::cplx* d_tw[kMaxLog2P + 1] = {};
   int* d_pos[kMaxLog2P + 1] = {};           // padded DIT input positions per FFT length (em_fft.cuh: pos_tab)
@@ -279,6 +296,8 @@ namespace {
 
 int set_device(proton_em_ctx* ctx) {
   CU_TRY(cudaSetDevice(ctx->device));
+  tl_pool = ctx->pool;
+  tl_stream = ctx->stream;
   return PROTON_EM_OK;
 }
 
@@ -655,6 +674,24 @@ int proton_em_create(proton_em_ctx** out, int device) {
   CU_TRY(cudaGetDeviceProperties(&prop, device));
   ctx->sm_count = prop.multiProcessorCount;
   CU_TRY(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  {
+    const char* e = std::getenv("PROTON_EM_ASYNC_ALLOC");
+    if (!(e && std::atoi(e) == 0)) {
+      cudaMemPoolProps props = {};
+      props.allocType = cudaMemAllocationTypePinned;
+      props.location.type = cudaMemLocationTypeDevice;
+      props.location.id = device;
+      if (cudaMemPoolCreate(&ctx->pool, &props) == cudaSuccess) {
+        unsigned long long keep = ~0ULL;                    // freed blocks stay in the pool until the context goes
+        cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      } else {
+        ctx->pool = nullptr;                                // no pool support: plain cudaMalloc / cudaFree
+        cudaGetLastError();
+      }
+    }
+    tl_pool = ctx->pool;
+    tl_stream = ctx->stream;
+  }
   for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
     CU_TRY(cudaStreamCreateWithFlags(&ctx->lane[i], cudaStreamNonBlocking));
     CU_TRY(cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
@@ -720,6 +757,8 @@ int proton_em_destroy(proton_em_ctx* ctx) {
   if (!ctx) return PROTON_EM_OK;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  tl_pool = nullptr;                                        // the device is idle: plain cudaFree for what is left
+  tl_stream = nullptr;
   for (int i = 0; i < proton_em_ctx::kLanes; ++i) {
     if (ctx->lane[i]) cudaStreamDestroy(ctx->lane[i]);
     if (ctx->ev_join[i]) cudaEventDestroy(ctx->ev_join[i]);
@@ -742,6 +781,7 @@ int proton_em_destroy(proton_em_ctx* ctx) {
   ctx->long_x.free(); ctx->long_y.free(); ctx->long_part_v.free(); ctx->long_part_i.free();
   ctx->long_tr_line.free(); ctx->long_tr_pair.free();
   ctx->arena.release();
+  if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
   delete ctx;
   return PROTON_EM_OK;
 }
@@ -783,7 +823,7 @@ int proton_em_profile_read(const proton_em_ctx* ctx, int kind, const char** name
 }
 
 int proton_em_plan_destroy(proton_em_plan* plan) {
-  if (plan && plan->ctx) { cudaSetDevice(plan->ctx->device); cudaStreamSynchronize(plan->ctx->stream); }
+  if (plan && plan->ctx) { set_device(plan->ctx); cudaStreamSynchronize(plan->ctx->stream); }
   destroy_plan(plan);
   return PROTON_EM_OK;
 }
