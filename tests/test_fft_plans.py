@@ -1,0 +1,64 @@
+"""The shared-memory layout of the in-CTA transforms (proton_b200/csrc/em_fft.cuh) rests on two properties of the index
+padding that the kernels use without checking: (1) the padded distance between the elements of a butterfly does not
+depend on the butterfly (so the offsets are compile-time immediates, `pad_off`), and (2) the 16-byte accesses of a
+quarter-warp fall into different bank groups.  This mirrors plan_radix / pad_idx of the header and checks both by brute
+force for every transform length the library instantiates (CPU only)."""
+import pytest
+
+
+def lg2(r):
+    return {2: 1, 4: 2, 8: 3, 16: 4}[r]
+
+
+def plan(log2p):                      # em_fft.cuh: plan16 / plan_n / plan_radix
+    if log2p in (12, 13):
+        n = log2p // 4 + (1 if log2p % 4 else 0)
+        return [16 if i < log2p // 4 else {1: 2, 2: 4, 3: 8}[log2p % 4] for i in range(n)]
+    n = log2p // 3 + (1 if log2p % 3 else 0)
+    return [8 if i < log2p // 3 else (2 if log2p % 3 == 1 else 4) for i in range(n)]
+
+
+def pad(log2p, p):                    # em_fft.cuh: pad_sh1 / pad_sh2 / pad_idx_rt
+    pl = plan(log2p)
+    sh1 = 4 if pl[-1] == 16 else 3
+    sh2 = log2p - lg2(pl[0])
+    return p + (p >> sh1) + (p >> sh2)
+
+
+def worst_conflict(addrs):            # 16-byte elements: 8 lanes per wavefront, bank group = address mod 8
+    worst = 1
+    for i in range(0, len(addrs), 8):
+        cnt = {}
+        for a in set(addrs[i:i + 8]):
+            cnt[a % 8] = cnt.get(a % 8, 0) + 1
+        worst = max(worst, max(cnt.values()))
+    return worst
+
+
+@pytest.mark.parametrize("log2p", range(6, 14))
+def test_padding_identity_and_bank_conflicts(log2p):
+    P = 1 << log2p
+    pl = plan(log2p)
+    assert sum(lg2(r) for r in pl) == log2p
+    s = log2p
+    for R in pl:
+        s -= lg2(R)
+        S, NB = 1 << s, P // R
+        for b in range(NB):
+            j = b & (S - 1)
+            base = ((b >> s) << (s + lg2(R))) | j
+            for q in range(R):
+                assert pad(log2p, base + q * S) == pad(log2p, base) + pad(log2p, q * S), (log2p, R, S, b, q)
+        worst = 1
+        for q in range(R):
+            for b0 in range(0, NB - NB % 32 or NB, 32):
+                addrs = []
+                for b in range(b0, min(b0 + 32, NB)):
+                    j = b & (S - 1)
+                    addrs.append(pad(log2p, (((b >> s) << (s + lg2(R))) | j) + q * S))
+                worst = max(worst, worst_conflict(addrs))
+        # at most a 2-way conflict, and only in the innermost stages (stride <= 4) of the plans that end in radix 2 or 4 (and of the 64-point plan)
+        assert worst == 1 or (worst == 2 and S <= 4 and (pl[-1] < 8 or log2p == 6)), (log2p, R, S, worst)
+    # natural-order access (modal phase of Bluestein, staging) is conflict-free
+    assert max(worst_conflict([pad(log2p, k) for k in range(k0, k0 + 32)]) for k0 in range(0, P, 32)) == 1
+    assert pad(log2p, P - 1) + 1 <= ((pad(log2p, P - 1) + 8) & ~7)      # padded_len()
