@@ -211,9 +211,16 @@ template <int RADIX, int SIGN> __device__ __forceinline__ void twiddle_jit(cplx 
 // Shared-memory index padding (units of 16-byte complex): one pad slot per 8 (16 when the innermost radix is 16)
 // elements keeps the stride-R accesses of the s = 1 stages conflict-free, one more per P/R0 elements does the same
 // for the digit-reversed scatter of the power-of-two path (checked by brute force for every plan).
+// Shifts found by exhaustive search per plan (tests/test_fft_plans.py repeats the check): every stage, the natural-order
+// accesses and the digit-reversed scatter are free of bank conflicts for each of them.
 __host__ __device__ constexpr int pad_sh1(int log2p) { return plan_radix(log2p, plan_n(log2p) - 1) == 16 ? 4 : 3; }
-__host__ __device__ constexpr int pad_sh2(int log2p) { return log2p - lg2(plan_radix(log2p, 0)); }
-__host__ __device__ constexpr int pad_idx_rt(int log2p, int p) { return p + (p >> pad_sh1(log2p)) + (p >> pad_sh2(log2p)); }
+__host__ __device__ constexpr int pad_sh2(int log2p) {
+  return log2p == 6 ? 0 : (log2p == 7 || log2p == 8) ? 6 : log2p - lg2(plan_radix(log2p, 0));
+}
+__host__ __device__ constexpr int pad_sh3(int log2p) { return (log2p == 13 && plan16(13)) ? 4 : 0; }
+__host__ __device__ constexpr int pad_idx_rt(int log2p, int p) {
+  return p + (p >> pad_sh1(log2p)) + (pad_sh2(log2p) ? (p >> pad_sh2(log2p)) : 0) + (pad_sh3(log2p) ? (p >> pad_sh3(log2p)) : 0);
+}
 template <int LOG2P> __host__ __device__ constexpr int pad_idx(int p) { return pad_idx_rt(LOG2P, p); }
 template <int LOG2P> __host__ __device__ constexpr int padded_len() { return (pad_idx_rt(LOG2P, (1 << LOG2P) - 1) + 8) & ~7; }
 

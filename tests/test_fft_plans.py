@@ -18,11 +18,21 @@ def plan(log2p):                      # em_fft.cuh: plan16 / plan_n / plan_radix
     return [8 if i < log2p // 3 else (2 if log2p % 3 == 1 else 4) for i in range(n)]
 
 
-def pad(log2p, p):                    # em_fft.cuh: pad_sh1 / pad_sh2 / pad_idx_rt
+def pad(log2p, p):                    # em_fft.cuh: pad_sh1 / pad_sh2 / pad_sh3 / pad_idx_rt
     pl = plan(log2p)
     sh1 = 4 if pl[-1] == 16 else 3
-    sh2 = log2p - lg2(pl[0])
-    return p + (p >> sh1) + (p >> sh2)
+    sh2 = 0 if log2p == 6 else 6 if log2p in (7, 8) else log2p - lg2(pl[0])
+    sh3 = 4 if log2p == 13 else 0
+    return p + (p >> sh1) + ((p >> sh2) if sh2 else 0) + ((p >> sh3) if sh3 else 0)
+
+
+def digit_pos(log2p, k):              # em_fft.cuh: digit_pos
+    pos, sh = 0, log2p
+    for r in plan(log2p):
+        sh -= lg2(r)
+        pos |= (k & (r - 1)) << sh
+        k >>= lg2(r)
+    return pos
 
 
 def worst_conflict(addrs):            # 16-byte elements: 8 lanes per wavefront, bank group = address mod 8
@@ -57,8 +67,8 @@ def test_padding_identity_and_bank_conflicts(log2p):
                     j = b & (S - 1)
                     addrs.append(pad(log2p, (((b >> s) << (s + lg2(R))) | j) + q * S))
                 worst = max(worst, worst_conflict(addrs))
-        # at most a 2-way conflict, and only in the innermost stages (stride <= 4) of the plans that end in radix 2 or 4 (and of the 64-point plan)
-        assert worst == 1 or (worst == 2 and S <= 4 and (pl[-1] < 8 or log2p == 6)), (log2p, R, S, worst)
-    # natural-order access (modal phase of Bluestein, staging) is conflict-free
+        assert worst == 1, (log2p, R, S, worst)
+    # the digit-reversed scatter of the power-of-two path and the natural-order accesses are conflict-free too
+    assert max(worst_conflict([pad(log2p, digit_pos(log2p, k)) for k in range(k0, k0 + 32)]) for k0 in range(0, P, 32)) == 1
     assert max(worst_conflict([pad(log2p, k) for k in range(k0, k0 + 32)]) for k0 in range(0, P, 32)) == 1
     assert pad(log2p, P - 1) + 1 <= ((pad(log2p, P - 1) + 8) & ~7)      # padded_len()
