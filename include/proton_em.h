@@ -77,7 +77,7 @@ typedef struct proton_em_result {
 
 /* Context: one per (process, device); owns a stream, the constant tables and a cache of per-length
  * tables (lambda_k from the host libm, chirps, transformed chirps).  Not thread-safe; distinct
- * contexts are independent. */
+ * contexts are independent.  Plans point into their context: destroy every plan before its context. */
 int proton_em_create(proton_em_ctx** out, int device);
 int proton_em_destroy(proton_em_ctx* ctx);
 const char* proton_em_last_error(void);
@@ -86,7 +86,11 @@ const char* proton_em_version(void);
 /* Pack: validates the batch, computes r = B*u per line and the forward DCT, and leaves the
  * time-independent modal weights resident in device memory.  Replaces form_analytical_solution +
  * dct1d (bin/EMtool_analytical@0xc46c, @0xc156).  `location` says where the batch arrays live.
- * Synchronous (it builds host-side tables and reports input errors). */
+ * Synchronous (it builds host-side tables and reports input errors).
+ * Line length limit of this build: num_nodes <= 65536 for any length, and the powers of two up to 131072; a longer
+ * line is rejected with PROTON_EM_EINVAL and a message naming it (the reference has no such limit in principle, but
+ * its dense N x N matrices stop it near N = 30 000 on a 16 GB host).  The same limit holds for proton_em_run_cfg and
+ * proton_em_analyze_host. */
 int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* batch, int location, proton_em_plan** out);
 int proton_em_plan_destroy(proton_em_plan* plan);
 int64_t proton_em_plan_total_nodes(const proton_em_plan* plan);
@@ -151,8 +155,10 @@ int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_
  * PROTON_EM_EINVAL.  The call queues its kernels on `stream` (a cudaStream_t, NULL = default stream),
  * then waits for them, so results are ready on return.  Every call shares the one array and leaves its
  * contents there: calls whose GPU work could overlap (other streams or threads, same device) race and must
- * be serialised by the caller.  The first call on a device looks up the array's address; make it before
- * starting any stream capture.  Uses the O(N^2) direct evaluator, so it is meant for single lines, not bulk. */
+ * be serialised by the caller.  Host side: the lambda table is staged through a per-thread host buffer, so threads
+ * that serve different devices do not disturb each other; the caller's current device is restored on return.
+ * The first call on a device looks up the array's address; make it before starting any stream capture.
+ * Uses the O(N^2) direct evaluator, so it is meant for single lines, not bulk. */
 int proton_em_eval_line_noalloc(int device, void* stream, int32_t num_nodes, double a_coeff,
                                 int32_t num_triplets, const int32_t* d_trip_row, const int32_t* d_trip_col,
                                 const double* d_trip_val, int32_t num_curden, const double* d_curden,

@@ -8,6 +8,7 @@ device (torch CUDA tensor) entry points are separate so nothing is copied behind
 from __future__ import annotations
 
 import ctypes
+import weakref
 from dataclasses import dataclass
 from typing import Iterable, Optional, Sequence
 
@@ -117,9 +118,12 @@ class Context:
         self._h = ctypes.c_void_p()
         check(self._lib.proton_em_create(ctypes.byref(self._h), int(device)))
         self.device = int(device)
+        self._plans = weakref.WeakSet()     # live plans: they hold pointers into the context and must go first
 
     def close(self):
         if self._h:
+            for plan in list(self._plans):
+                plan.close()
             self._lib.proton_em_destroy(self._h)
             self._h = ctypes.c_void_p()
 
@@ -241,6 +245,7 @@ class Plan:
         self._h = handle
         self.node_off = node_off
         self._keep = keep
+        ctx._plans.add(self)
 
     @property
     def num_lines(self) -> int:
@@ -256,7 +261,8 @@ class Plan:
 
     def close(self):
         if self._h:
-            self.ctx._lib.proton_em_plan_destroy(self._h)
+            if self.ctx._h:                      # a context that is already gone took its plans with it
+                self.ctx._lib.proton_em_plan_destroy(self._h)
             self._h = ctypes.c_void_p()
 
     def __del__(self):

@@ -50,7 +50,6 @@ struct EvalParams {
   const double* W;             // [sum N] folded modal weights (forward kernel)
   const double* ts;            // [T]
   const cplx* tw;              // base twiddles of this P, per stage (stage_tw_offset)
-  const ulonglong2* exp_tab;   // [128]
   const int* pos_tab;          // [P] padded shared-memory position of spectrum entry k for the DIT input (pow2 classes)
   double* stress;              // may be null (reduce-only)
   double* mx;                  // [L*T]
@@ -261,7 +260,7 @@ template <int LOG2P, bool BLUE> struct Cfg {
   static constexpr size_t data_bytes = (size_t)G * padded_len<LOG2P>() * sizeof(cplx);
   static constexpr size_t stage_bytes = ALIAS_STAGE ? 0 : (size_t)G * 2 * NSTAGE * sizeof(double);
   static constexpr size_t tw_bytes = (size_t)stage_tw_total(LOG2P) * sizeof(cplx);
-  static constexpr size_t head_bytes = kExpTableEntries * sizeof(ulonglong2) + tw_bytes;
+  static constexpr size_t head_bytes = tw_bytes;
   static constexpr size_t smem_bytes = head_bytes + data_bytes + stage_bytes;
 };
 
@@ -481,13 +480,11 @@ em_eval_fft_kernel(const EvalParams prm) {
   constexpr int P = C::P, NT = C::NT, G = C::G, NST = plan_n(LOG2P);
   constexpr int TSTRIDE = padded_len<LOG2P>();
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  ulonglong2* exp_tab = reinterpret_cast<ulonglong2*>(smem_raw);
-  cplx* twb = reinterpret_cast<cplx*>(smem_raw + kExpTableEntries * sizeof(ulonglong2));
+  cplx* twb = reinterpret_cast<cplx*>(smem_raw);
   cplx* data = reinterpret_cast<cplx*>(smem_raw + C::head_bytes);
   double* stage = C::ALIAS_STAGE ? reinterpret_cast<double*>(data)
                                  : reinterpret_cast<double*>(smem_raw + C::head_bytes + C::data_bytes);
   const int tid = threadIdx.x;
-  for (int i = tid; i < kExpTableEntries; i += NT) exp_tab[i] = prm.exp_tab[i];
   for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = prm.tw[i];
 
   const int item = blockIdx.x;
@@ -531,10 +528,10 @@ em_eval_fft_kernel(const EvalParams prm) {
           const double t2 = (j1 + 1 < T) ? prm.ts[j1 + 1] : t1;
           const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
           cplx* d = data + g * TSTRIDE;
-          const double y1k = em_modal(lamk, wk, w1, t1, exp_tab);
-          const double y2k = em_modal(lamk, wk, w2, t2, exp_tab);
-          const double y1kk = em_modal(lamkk, wkk, w1, t1, exp_tab);
-          const double y2kk = em_modal(lamkk, wkk, w2, t2, exp_tab);
+          const double y1k = em_modal(lamk, wk, w1, t1);
+          const double y2k = em_modal(lamk, wk, w2, t2);
+          const double y1kk = em_modal(lamkk, wkk, w1, t1);
+          const double y2kk = em_modal(lamkk, wkk, w2, t2);
           d[posk] = cmul(prek, cplx{y1k + y2kk, y2k - y1kk});
           d[poskk] = cmul(prekk, cplx{y1kk + y2k, y2kk - y1k});
         }
@@ -547,8 +544,8 @@ em_eval_fft_kernel(const EvalParams prm) {
           const double t1 = prm.ts[j1];
           const double t2 = (j1 + 1 < T) ? prm.ts[j1 + 1] : t1;
           const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
-          const double y1 = em_modal(lam[k], W[k], w1, t1, exp_tab);
-          const double y2 = em_modal(lam[k], W[k], w2, t2, exp_tab);
+          const double y1 = em_modal(lam[k], W[k], w1, t1);
+          const double y2 = em_modal(lam[k], W[k], w2, t2);
           const int posk = pad_idx<LOG2P>(BLUE ? k : digit_pos<LOG2P>(k));
           data[g * TSTRIDE + posk] = which ? cmul(ldg_cplx(tab.pre + k), cplx{y1 + y2, y2 - y1}) : cplx{y1, y2};
         }

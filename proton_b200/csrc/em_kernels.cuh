@@ -225,12 +225,7 @@ __global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT) em_tables_kernel(const T
   for (int i = tid; i < P; i += NT) hhat[i] = data[pad_idx<LOG2P>(i)];
 }
 
-// ---------------------------------------------------------------------------------------------
-// Short lines (N <= 32): one warp per (line, chunk of timestamps); lane n owns node n, lane k
-// evaluates mode k, a per-warp table holds cos(pi m / 2N), m in [0, 4N).
-// ---------------------------------------------------------------------------------------------
-constexpr int kSmallMaxN = 32;
-
+// Parameters of the short-line (dense) kernel.
 struct SmallParams {
   const int* class_lines;
   int n_class_lines;
@@ -253,69 +248,14 @@ struct SmallParams {
   int max_nodes;               // longest line of the class (sizes the dense kernel's shared memory)
 };
 
-__global__ void __launch_bounds__(128) em_eval_small_kernel(const SmallParams p) {
-  __shared__ ulonglong2 exp_tab[kExpTableEntries];
-  __shared__ double ctab[4][4 * kSmallMaxN];
-  for (int i = threadIdx.x; i < kExpTableEntries; i += blockDim.x) exp_tab[i] = p.exp_tab[i];
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long item = (long long)blockIdx.x * 4 + warp;
-  if (item >= (long long)p.n_class_lines * p.chunks) return;
-  const int li = (int)(item / p.chunks), chunk = (int)(item - (long long)li * p.chunks);
-  const int line = p.class_lines[li];
-  const int N = p.num_nodes[line];
-  const double a = p.a_coeff[line];
-  const long long noff = p.node_off[line];
-  double* ct = ctab[warp];
-  for (int m = lane; m < 4 * N; m += 32) ct[m] = em_cos_frac((unsigned long long)m, 2ULL * N);
-  __syncwarp();
-  double lam = 0.0, wk = 0.0;
-  if (lane < N) {
-    lam = p.tabs[p.line_tab[line]].lam[lane];
-    wk = p.W[noff + lane];
-    if (lane > 0) wk = wk + wk;     // W carries Makhoul's 1/2 for k >= 1; the plain cosine sum does not want it
-  }
-  const int j0 = chunk * p.ts_per_chunk, j1 = min(p.T, j0 + p.ts_per_chunk);
-  const int step = 2 * lane + 1;
-  const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
-  for (int j = j0; j < j1; ++j) {
-    const double t = p.ts[j];
-    const double w = __dmul_rn(a, t);
-    const double y = (lane < N) ? em_modal(lam, wk, w, t, exp_tab) : 0.0;
-    double acc = 0.0;
-    int m = 0;
-    for (int k = 0; k < N; ++k) {
-      const double yk = __shfl_sync(0xffffffffu, y, k);
-      if (lane < N) acc = fma(yk, ct[m], acc);
-      m += step;
-      if (m >= 4 * N) m -= 4 * N;
-    }
-    double best = ninf;
-    int besti = 0x7fffffff;
-    if (lane < N && acc > ninf) { best = acc; besti = lane; }
-    if (p.stress && lane < N) __stcs(p.stress + noff * (long long)p.T + (long long)j * N + lane, acc);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const double ob = __shfl_xor_sync(0xffffffffu, best, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
-      if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
-    }
-    const double first = __shfl_sync(0xffffffffu, acc, 0);
-    if (lane == 0) {
-      if (besti == 0x7fffffff) { besti = 0; best = first; }
-      const long long o = (long long)line * p.T + j;
-      p.mx[o] = best; p.amx[o] = besti; p.flag[o] = (best > p.critical) ? 1 : 0;
-    }
-  }
-}
-
 // ---------------------------------------------------------------------------------------------
 // Direct O(N^2) evaluator for any N: one CTA per (line, timestamp).  Not a production path — it is
 // the device-side cross-check the tests use (opts.algorithm = DIRECT), with every cosine obtained
 // from an exactly reduced angle.
 // ---------------------------------------------------------------------------------------------
 struct DirectParams {
-  long long num_lines;
+  long long num_lines;         // lines of this launch
+  long long line0;             // first line of this launch (a launch covers the contiguous lines of its chunks)
   int T;
   const int* num_nodes;
   const double* a_coeff;
@@ -341,8 +281,9 @@ __global__ void __launch_bounds__(256) em_eval_direct_kernel(const DirectParams 
   __shared__ double first_s;
   for (int i = threadIdx.x; i < kExpTableEntries; i += blockDim.x) exp_tab[i] = p.exp_tab[i];
   __syncthreads();
-  const long long line = blockIdx.x / p.T;
-  const int j = (int)(blockIdx.x - line * p.T);
+  const long long rel = blockIdx.x / p.T;
+  const int j = (int)(blockIdx.x - rel * p.T);
+  const long long line = p.line0 + rel;
   const int N = p.num_nodes[line];
   const double a = p.a_coeff[line];
   const long long noff = p.node_off[line];
@@ -468,7 +409,7 @@ __global__ void __launch_bounds__(128) em_eval_dense_kernel(const SmallParams p)
       if (k < N && tvalid) {
         double wk = W[k];
         if (k > 0) wk = wk + wk;              // W carries Makhoul's 1/2 for k >= 1; the plain cosine sum does not want it
-        b = em_modal(lam[k], wk, w, tt, nullptr);
+        b = em_modal(lam[k], wk, w, tt);
       }
       const double* af = afrag + ks * 32 + lane;
 #pragma unroll

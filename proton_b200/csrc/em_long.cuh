@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
       yk[q] = cplx{0.0, 0.0};
       if (active && q < P1 && k < N) {
         const double l = tab.lam[k], wk = W[k];
-        yk[q] = cplx{em_modal(l, wk, w1, t1, nullptr), em_modal(l, wk, w2, t2, nullptr)};
+        yk[q] = cplx{em_modal(l, wk, w1, t1), em_modal(l, wk, w2, t2)};
       }
       ys[q * 128 + tid] = yk[q];
     }
@@ -327,12 +327,12 @@ __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) 
   const double* __restrict__ lam = tab.lam;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; 2 * k <= N; k += gridDim.x * blockDim.x) {
     const double l = lam[k], wk = W[k];
-    const double y1 = em_modal(l, wk, w1, t1, nullptr), y2 = em_modal(l, wk, w2, t2, nullptr);
+    const double y1 = em_modal(l, wk, w1, t1), y2 = em_modal(l, wk, w2, t2);
     if (k == 0) { x[long_pos<LOG2P1>(0)] = cplx{y1, y2}; continue; }
     const int kk = N - k;
     if (kk == k) { x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(tab.pre + k), cplx{y1 + y2, y2 - y1}); continue; }
     const double lm = lam[kk], wm = W[kk];
-    const double m1 = em_modal(lm, wm, w1, t1, nullptr), m2 = em_modal(lm, wm, w2, t2, nullptr);
+    const double m1 = em_modal(lm, wm, w1, t1), m2 = em_modal(lm, wm, w2, t2);
     x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(tab.pre + k), cplx{y1 + m2, y2 - m1});
     x[long_pos<LOG2P1>(kk)] = cmul(ldg_cplx(tab.pre + kk), cplx{m1 + y2, m2 - y1});
   }

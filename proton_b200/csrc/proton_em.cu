@@ -8,8 +8,7 @@
 //   other N <= 65536, 2^p <= 131072   em_long_{colfwd_paired | scatter} -> em_long_row -> em_long_colinv
 //                                (P = P1 x 4096 through an L2-resident scratch, waves dealt to `lanes` streams)
 // Tuning knobs, all optional environment variables read once: PROTON_EM_LANES (2), PROTON_EM_LONG_WAVE_MB (32),
-// PROTON_EM_PDL (1), PROTON_EM_COL_DIV (48), PROTON_EM_DENSE_MAX (88), PROTON_EM_CHUNK_MB (256),
-// PROTON_EM_SMALL=table, PROTON_EM_TRACE.
+// PROTON_EM_PDL (1), PROTON_EM_COL_DIV (48), PROTON_EM_DENSE_MAX (88), PROTON_EM_CHUNK_MB (256), PROTON_EM_TRACE.
 // There is no CPU fallback: every entry point fails with PROTON_EM_ECUDA when no device is usable.
 #include "../../include/proton_em.h"
 
@@ -94,7 +93,7 @@ enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_LPOW2 = 3, CLS_L
 struct ClassOf { LineClass cls; int log2p; };
 
 // Lines up to this length take the dense (DMMA) path; the split against the FFT path is set from measured
-// throughput, PROTON_EM_DENSE_MAX overrides it for experiments (<= 64; the table kernel needs <= 32).
+// throughput, PROTON_EM_DENSE_MAX overrides it for experiments.
 int small_max_n() {
   static const int v = [] {
     const char* e = std::getenv("PROTON_EM_DENSE_MAX");
@@ -226,7 +225,7 @@ struct proton_em_ctx {
   DevBuf<unsigned char> io_flag;
   DevBuf<em::cplx> long_x, long_y;
   DevBuf<double> long_part_v;
-  DevBuf<int> long_part_i, long_tr_line, long_tr_pair;
+  DevBuf<int> long_part_i;
   // per-kernel timing (proton_em_profile): an event pair around every launch of the evaluation path
   bool prof_on = false;
   struct ProfRec { int kind; cudaEvent_t a, b; };
@@ -237,9 +236,9 @@ struct proton_em_ctx {
 };
 
 namespace {
-enum ProfKind { PK_DENSE = 0, PK_TABLE, PK_FFT_POW2, PK_FFT_BLUE, PK_LONG_COLFWD, PK_LONG_ROW, PK_LONG_COLINV,
+enum ProfKind { PK_DENSE = 0, PK_FFT_POW2, PK_FFT_BLUE, PK_LONG_COLFWD, PK_LONG_ROW, PK_LONG_COLINV,
                 PK_LONG_SCATTER, PK_LONG_REDUCE, PK_COUNT };
-const char* const kProfNames[PK_COUNT] = {"em_eval_dense_kernel", "em_eval_small_kernel", "em_eval_fft_kernel<pow2>",
+const char* const kProfNames[PK_COUNT] = {"em_eval_dense_kernel", "em_eval_fft_kernel<pow2>",
                                           "em_eval_fft_kernel<bluestein>", "em_long_colfwd_paired_kernel",
                                           "em_long_row_kernel", "em_long_colinv_kernel", "em_long_scatter_kernel",
                                           "em_long_reduce_kernel"};
@@ -288,6 +287,10 @@ struct proton_em_plan {
   struct Chunk { int64_t l0, l1; std::vector<ClassList> classes; };
   std::vector<Chunk> chunks;
   std::vector<int> h_class_lines;    // host copy of d_class_lines
+  // long-line transform lists (slot -> line, timestamp pair): they depend on (T, chunk range) only, so they are
+  // built and uploaded once and reused by every later evaluation of the plan
+  struct LongList { int T, c0, c1; long long n; DevBuf<int> line, pair; };
+  std::vector<LongList*> long_lists;
   std::vector<long long> node_off;   // host copy
   std::vector<int> num_nodes;        // host copy
 };
@@ -412,14 +415,14 @@ int ensure_long(proton_em_ctx* ctx, int p1, int cap, long long n_tr_total) {
     CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_twl[p1]), n * sizeof(em::cplx)));
     em::em_long_twiddle_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_twl[p1], p1);
     ctx->launches++;
-    CU_TRY(cudaGetLastError());
-    CU_TRY(cudaStreamSynchronize(ctx->stream));     // the lanes read it without ordering against this stream
+    CU_TRY(cudaGetLastError());        // (the lanes fork from the context stream at every evaluation, so they see it)
   }
   const size_t lanes = (size_t)ctx->lanes;
   const size_t need_x = lanes * (size_t)cap * (size_t)p1 * em::kLongP2;
   const size_t need_p = (size_t)std::max<long long>(n_tr_total, 1) * 2 * kLongColBlocks;
   if (ctx->long_x.n < need_x || ctx->long_part_v.n < need_p) {
-    CU_TRY(cudaDeviceSynchronize());                // earlier waves may still use the old buffers
+    // Earlier waves may still use the old buffers: with the pool, release and allocation are ordered on the context
+    // stream, which every evaluation's lanes have joined; without it cudaFree synchronises by itself.
     if (ctx->long_x.n < need_x) CU_TRY(ctx->long_x.alloc(need_x));
     if (ctx->long_part_v.n < need_p) { CU_TRY(ctx->long_part_v.alloc(need_p)); CU_TRY(ctx->long_part_i.alloc(need_p)); }
   }
@@ -510,20 +513,17 @@ int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp
   return PROTON_EM_OK;
 }
 
-// pre / post chirps and the transformed chirp H of new long lengths (all entries share log2p and kind).
-int long_build_tables(proton_em_ctx* ctx, const std::vector<em::NTab>& entries, int lp1, bool blue) {
+// pre / post chirps and the transformed chirp H of new long lengths (`d_e`: device array of `count` entries that share
+// the row count and the kind).  Queued on the context stream, no host synchronisation.
+int long_build_tables(proton_em_ctx* ctx, const em::NTab* d_e, int count, int lp1, bool blue) {
   const int cap = long_wave_capacity(lp1);
   { int rc = ensure_long(ctx, lp1, cap, 1); if (rc) return rc; }
-  em::NTab* d_e = nullptr;
-  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&d_e), entries.size() * sizeof(em::NTab)));
-  struct G { em::NTab* p; ~G() { cudaFree(p); } } g{d_e};
-  CU_TRY(cudaMemcpyAsync(d_e, entries.data(), entries.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, ctx->stream));
-  em::em_long_prepost_kernel<<<dim3(64, (unsigned)entries.size()), 256, 0, ctx->stream>>>(d_e, blue ? 1 : 0);
+  em::em_long_prepost_kernel<<<dim3(64, (unsigned)count), 256, 0, ctx->stream>>>(d_e, blue ? 1 : 0);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   if (blue) {
-    for (size_t off = 0; off < entries.size(); off += cap) {
-      const int cnt = (int)std::min<size_t>(cap, entries.size() - off);
+    for (int off = 0; off < count; off += cap) {
+      const int cnt = std::min(cap, count - off);
       em::ColParams cp{};
       cp.w.n_tr = cnt; cp.w.x = ctx->long_x.p;
       cp.mode = 1; cp.tabs_build = d_e + off; cp.tr_per_cta = 1; cp.twl = ctx->d_twl[lp1];
@@ -532,7 +532,6 @@ int long_build_tables(proton_em_ctx* ctx, const std::vector<em::NTab>& entries, 
       { int rc = launch_long_row(ctx, ctx->stream, rp, cnt); if (rc) return rc; }
     }
   }
-  CU_TRY(cudaStreamSynchronize(ctx->stream));
   return PROTON_EM_OK;
 }
 
@@ -605,33 +604,37 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
     }
     entries[i] = t;
   }
-  for (int blue = 0; blue < 2; ++blue) {
+  // One upload of all new entries (grouped by kernel), then one table launch per group, all on the context stream
+  // and without host synchronisation in between.
+  std::vector<em::NTab> sorted;
+  sorted.reserve(entries.size());
+  struct Group { int blue, key; size_t off, cnt; bool is_long; };
+  std::vector<Group> groups;
+  for (int blue = 0; blue < 2; ++blue)
     for (int p = kMinLog2P; p <= kMaxLog2P; ++p) {
-      std::vector<em::NTab> grp;
+      const size_t off = sorted.size();
       for (const em::NTab& t : entries)
-        if (t.log2p == p && t.bluestein == blue) grp.push_back(t);
-      if (grp.empty()) continue;
-      em::NTab* d_grp = nullptr;
-      CU_TRY(cudaMalloc(reinterpret_cast<void**>(&d_grp), grp.size() * sizeof(em::NTab)));
-      cudaError_t e = cudaMemcpyAsync(d_grp, grp.data(), grp.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, ctx->stream);
-      int rc = PROTON_EM_OK;
-      if (e == cudaSuccess) rc = blue ? launch_tables<true>(ctx, p, d_grp, (int)grp.size())
-                                      : launch_tables<false>(ctx, p, d_grp, (int)grp.size());
-      cudaError_t e2 = cudaStreamSynchronize(ctx->stream);
-      cudaFree(d_grp);
-      if (e != cudaSuccess) CU_TRY(e);
-      if (rc) return rc;
-      CU_TRY(e2);
+        if (t.log2p == p && t.bluestein == blue) sorted.push_back(t);
+      if (sorted.size() > off) groups.push_back({blue, p, off, sorted.size() - off, false});
     }
-  }
-  for (int blue = 0; blue < 2; ++blue) {
+  for (int blue = 0; blue < 2; ++blue)
     for (int p1 = 3; p1 <= em::kLongMaxP1; ++p1) {
-      std::vector<em::NTab> grp;
+      const size_t off = sorted.size();
       for (const em::NTab& t : entries)
-        if (t.p1 == p1 && t.bluestein == blue) grp.push_back(t);
-      if (grp.empty()) continue;
-      int rc = long_build_tables(ctx, grp, p1, blue != 0);
-      if (rc) return rc;
+        if (t.p1 == p1 && t.bluestein == blue) sorted.push_back(t);
+      if (sorted.size() > off) groups.push_back({blue, p1, off, sorted.size() - off, true});
+    }
+  if (!sorted.empty()) {
+    void* d_sorted_v = nullptr;
+    CU_TRY(ctx->arena.alloc(&d_sorted_v, sorted.size() * sizeof(em::NTab)));
+    em::NTab* d_sorted = static_cast<em::NTab*>(d_sorted_v);
+    CU_TRY(cudaMemcpyAsync(d_sorted, sorted.data(), sorted.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, ctx->stream));
+    for (const Group& g : groups) {
+      int rc;
+      if (g.is_long) rc = long_build_tables(ctx, d_sorted + g.off, (int)g.cnt, g.key, g.blue != 0);
+      else rc = g.blue ? launch_tables<true>(ctx, g.key, d_sorted + g.off, (int)g.cnt)
+                       : launch_tables<false>(ctx, g.key, d_sorted + g.off, (int)g.cnt);
+      if (rc) { cudaStreamSynchronize(ctx->stream); return rc; }
     }
   }
   CU_TRY(cudaStreamSynchronize(ctx->stream));   // lam upload must finish before `lam` goes away
@@ -648,6 +651,7 @@ void destroy_plan(proton_em_plan* p) {
   p->own_num_nodes.free(); p->own_a.free(); p->own_trip_off.free();
   p->d_node_off.free(); p->d_blk_off.free(); p->d_r_idx.free(); p->d_r_cnt.free(); p->d_line_tab.free();
   p->d_r_val.free(); p->d_W.free(); p->d_tabs.free(); p->d_class_lines.free();
+  for (auto* ll : p->long_lists) { ll->line.free(); ll->pair.free(); delete ll; }
   delete p;
 }
 
@@ -779,7 +783,6 @@ int proton_em_destroy(proton_em_ctx* ctx) {
   for (auto* p : ctx->d_pos) if (p) cudaFree(p);
   for (auto* p : ctx->d_twl) if (p) cudaFree(p);
   ctx->long_x.free(); ctx->long_y.free(); ctx->long_part_v.free(); ctx->long_part_i.free();
-  ctx->long_tr_line.free(); ctx->long_tr_pair.free();
   ctx->arena.release();
   if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
   delete ctx;
@@ -1036,7 +1039,8 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
 // round-robin to the lanes (streams) so that small waves of different classes overlap; one join, one reduction.
 static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_plan::ClassList*>& longs,
                          const double* d_ts, int T, double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag,
-                         double critical, long long* n_tr_out) {
+                         double critical, long long* n_tr_out, int chunk_begin, int chunk_end,
+                         const proton_em_plan::LongList** list_out) {
   proton_em_ctx* ctx = p->ctx;
   const int npairs = (T + 1) / 2;
   long long n_tr_total = 0;
@@ -1049,22 +1053,32 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
     if (rc) return rc;
     max_cap_p1 = std::max(max_cap_p1, cap * cl->log2p);
   }
-  std::vector<int> tr_line((size_t)n_tr_total), tr_pair((size_t)n_tr_total);
-  {
+  proton_em_plan::LongList* ll = nullptr;
+  for (auto* c : p->long_lists)
+    if (c->T == T && c->c0 == chunk_begin && c->c1 == chunk_end) { ll = c; break; }
+  if (!ll) {
+    std::vector<int> tr_line((size_t)n_tr_total), tr_pair((size_t)n_tr_total);
     size_t o = 0;
     for (const auto* cl : longs)
       for (int i = 0; i < cl->count; ++i) {
         const int line = p->h_class_lines[cl->offset + i];
         for (int pr = 0; pr < npairs; ++pr, ++o) { tr_line[o] = line; tr_pair[o] = pr; }
       }
+    if (p->long_lists.size() >= 8) {            // a plan evaluated at many different T: drop the oldest list
+      proton_em_plan::LongList* old = p->long_lists.front();
+      p->long_lists.erase(p->long_lists.begin());
+      old->line.free(); old->pair.free();       // stream-ordered: earlier evaluations on ctx->stream are done with it
+      delete old;
+    }
+    ll = new proton_em_plan::LongList();
+    ll->T = T; ll->c0 = chunk_begin; ll->c1 = chunk_end; ll->n = n_tr_total;
+    p->long_lists.push_back(ll);
+    CU_TRY(ll->line.alloc((size_t)n_tr_total));
+    CU_TRY(ll->pair.alloc((size_t)n_tr_total));
+    CU_TRY(cudaMemcpyAsync(ll->line.p, tr_line.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CU_TRY(cudaMemcpyAsync(ll->pair.p, tr_pair.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
   }
-  if (ctx->long_tr_line.n < (size_t)n_tr_total) {
-    CU_TRY(cudaDeviceSynchronize());
-    CU_TRY(ctx->long_tr_line.alloc((size_t)n_tr_total));
-    CU_TRY(ctx->long_tr_pair.alloc((size_t)n_tr_total));
-  }
-  CU_TRY(cudaMemcpyAsync(ctx->long_tr_line.p, tr_line.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-  CU_TRY(cudaMemcpyAsync(ctx->long_tr_pair.p, tr_pair.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  *list_out = ll;
   // fork: the lanes start after everything queued so far on the main stream (uploads above included)
   CU_TRY(cudaEventRecord(ctx->ev_fork, ctx->stream));
   for (int i = 0; i < ctx->lanes; ++i) CU_TRY(cudaStreamWaitEvent(ctx->lane[i], ctx->ev_fork, 0));
@@ -1084,7 +1098,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
       cudaStream_t st = ctx->lane[li];
       em::cplx* xbuf = ctx->long_x.p + (size_t)li * lane_stride;
       em::LongWave w{};
-      w.tr_line = ctx->long_tr_line.p + base + s0; w.tr_pair = ctx->long_tr_pair.p + base + s0; w.n_tr = cnt; w.T = T;
+      w.tr_line = ll->line.p + base + s0; w.tr_pair = ll->pair.p + base + s0; w.n_tr = cnt; w.T = T;
       w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
       w.tabs = p->d_tabs.p; w.W = p->d_W.p; w.ts = d_ts; w.exp_tab = ctx->d_exp;
       w.x = xbuf; w.stress = d_stress; w.tr_base = (int)(base + s0);
@@ -1114,8 +1128,8 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
 
 // Join of the lanes and the one reduction of the column-block partials (queued after the other classes so that
 // their kernels overlap the long waves).
-static int eval_long_finish(proton_em_plan* p, long long n_tr_total, int T, double* d_stress, double* d_mx, int* d_amx,
-                            unsigned char* d_flag, double critical) {
+static int eval_long_finish(proton_em_plan* p, const proton_em_plan::LongList* ll, long long n_tr_total, int T,
+                            double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag, double critical) {
   proton_em_ctx* ctx = p->ctx;
   for (int i = 0; i < ctx->lanes; ++i) {
     CU_TRY(cudaEventRecord(ctx->ev_join[i], ctx->lane[i]));
@@ -1123,7 +1137,7 @@ static int eval_long_finish(proton_em_plan* p, long long n_tr_total, int T, doub
   }
   if (n_tr_total <= 0) return PROTON_EM_OK;
   em::LongWave w{};
-  w.tr_line = ctx->long_tr_line.p; w.tr_pair = ctx->long_tr_pair.p; w.n_tr = (int)n_tr_total; w.T = T;
+  w.tr_line = ll->line.p; w.tr_pair = ll->pair.p; w.n_tr = (int)n_tr_total; w.T = T;
   w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
   w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
   w.critical = critical;
@@ -1143,10 +1157,14 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
   const double critical = opts ? opts->critical_stress : NAN;
   const int alg = opts ? opts->algorithm : PROTON_EM_ALG_AUTO;
   if (alg == PROTON_EM_ALG_DIRECT) {
-    if ((long long)p->L * T > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "direct algorithm: L*T too large");
-    em::DirectParams dp{p->L, T, p->d_num_nodes, p->d_a, p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p,
+    // only the lines of the chunks asked for: the host paths hand in a stress pointer that is valid for one chunk
+    const int c_end = chunk_end < 0 ? (int)p->chunks.size() : chunk_end;
+    if (chunk_begin >= c_end) return PROTON_EM_OK;
+    const long long l0 = p->chunks[chunk_begin].l0, l1 = p->chunks[c_end - 1].l1;
+    if ((l1 - l0) * T > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "direct algorithm: L*T too large");
+    em::DirectParams dp{l1 - l0, l0, T, p->d_num_nodes, p->d_a, p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p,
                         d_ts, ctx->d_exp, d_stress, d_mx, d_amx, d_flag, critical};
-    em::em_eval_direct_kernel<<<(unsigned)(p->L * T), 256, 0, ctx->stream>>>(dp);
+    em::em_eval_direct_kernel<<<(unsigned)((l1 - l0) * T), 256, 0, ctx->stream>>>(dp);
     ctx->launches++;
     CU_TRY(cudaGetLastError());
     return PROTON_EM_OK;
@@ -1161,12 +1179,14 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
   // Every class kernel goes to one of the lanes (streams forked off the main stream) so that the tails of the
   // per-class launches overlap; the long lines' waves use the same lanes.  One join at the end.
   long long n_long_tr = 0;
+  const proton_em_plan::LongList* long_list = nullptr;
   int next_lane = 0;
   if (longs.empty()) {
     CU_TRY(cudaEventRecord(ctx->ev_fork, ctx->stream));
     for (int i = 0; i < ctx->lanes; ++i) CU_TRY(cudaStreamWaitEvent(ctx->lane[i], ctx->ev_fork, 0));
   } else {
-    int rc = eval_long_all(p, longs, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical, &n_long_tr);
+    int rc = eval_long_all(p, longs, d_ts, T, d_stress, d_mx, d_amx, d_flag, critical, &n_long_tr, chunk_begin, chunk_end,
+                           &long_list);
     if (rc) return rc;
   }
   for (int ci = chunk_begin; ci < chunk_end; ++ci)
@@ -1174,9 +1194,8 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
     if (cl.cls == CLS_LPOW2 || cl.cls == CLS_LBLUE) continue;
     cudaStream_t cst = ctx->lane[next_lane++ % ctx->lanes];
     if (cl.cls == CLS_SMALL) {
-      // dense contraction on the FP64 tensor cores (DMMA); PROTON_EM_SMALL=table selects the cosine-table kernel
-      static const bool use_table = [] { const char* e = std::getenv("PROTON_EM_SMALL"); return e && std::strcmp(e, "table") == 0 && small_max_n() <= em::kSmallMaxN; }();
-      if (!use_table) {
+      // dense contraction on the FP64 tensor cores (DMMA)
+      {
         // the class list is sorted longest first: cut it where the number of 8-node tiles drops to 8 and to 4
         int begin = 0;
         const int limits[3] = {64, 32, 0};
@@ -1206,20 +1225,6 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
         }
         continue;
       }
-      int chunks = (int)std::min<long long>(T, std::max<long long>(1, target_items * 4 / cl.count));
-      int tpc = (T + chunks - 1) / chunks;
-      chunks = (T + tpc - 1) / tpc;
-      em::SmallParams sp{p->d_class_lines.p + cl.offset, cl.count, chunks, tpc, T, p->d_num_nodes, p->d_a,
-                         p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_exp,
-                         d_stress, d_mx, d_amx, d_flag, critical, 0};
-      const long long items = (long long)cl.count * chunks;
-      {
-        ProfScope prof(ctx, PK_TABLE, cst);
-        em::em_eval_small_kernel<<<(unsigned)((items + 3) / 4), 128, 0, cst>>>(sp);
-      }
-      ctx->launches++;
-      CU_TRY(cudaGetLastError());
-      continue;
     }
     const bool blue = cl.cls == CLS_BLUE;
     const int G = fft_group(blue, cl.log2p);
@@ -1230,14 +1235,14 @@ static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proto
     ppc = ((ppc + G - 1) / G) * G;
     chunks = (npairs + ppc - 1) / ppc;
     em::EvalParams ep{p->d_class_lines.p + cl.offset, cl.count, chunks, ppc, T, p->d_num_nodes, p->d_a,
-                      p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_tw[cl.log2p], ctx->d_exp,
+                      p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_tw[cl.log2p],
                       ctx->d_pos[cl.log2p], d_stress, d_mx, d_amx, d_flag, critical};
     const long long grid = (long long)cl.count * chunks;
     if (grid > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many work items");
     int rc = launch_eval_fft(ctx, cst, blue, cl.log2p, ep, (int)grid);
     if (rc) return rc;
   }
-  return eval_long_finish(p, n_long_tr, T, d_stress, d_mx, d_amx, d_flag, critical);
+  return eval_long_finish(p, long_list, n_long_tr, T, d_stress, d_mx, d_amx, d_flag, critical);
 }
 
 int proton_em_eval(proton_em_plan* p, const double* ts, int32_t T, const proton_em_opts* opts,
@@ -1293,8 +1298,11 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const d
   const size_t LT = (size_t)L * T;
   int64_t max_nodes = 0;
   for (const auto& ch : plan->chunks) max_nodes = std::max<int64_t>(max_nodes, plan->node_off[ch.l1] - plan->node_off[ch.l0]);
-  if (ctx->io_stress[0].n < (size_t)max_nodes * T || ctx->io_mx.n < LT || ctx->io_ts.n < (size_t)T) {
-    CU_TRY(cudaDeviceSynchronize());
+  const size_t need_field = res->stress ? (size_t)max_nodes * T : 0;     // reduce-only calls need no staging field
+  if (ctx->io_stress[0].n < need_field || ctx->io_stress[1].n < need_field || ctx->io_mx.n < LT || ctx->io_ts.n < (size_t)T) {
+    // something has to grow: earlier work of this context may still use the old buffers
+    CU_TRY(cudaStreamSynchronize(ctx->stream));
+    CU_TRY(cudaStreamSynchronize(ctx->copy_stream));
     CU_TRY(grow(ctx->io_ts, (size_t)T)); CU_TRY(grow(ctx->io_mx, LT)); CU_TRY(grow(ctx->io_amx, LT)); CU_TRY(grow(ctx->io_flag, LT));
     if (res->stress) { CU_TRY(grow(ctx->io_stress[0], (size_t)max_nodes * T)); CU_TRY(grow(ctx->io_stress[1], (size_t)max_nodes * T)); }
   }
@@ -1377,7 +1385,11 @@ int proton_em_analyze_history_host(proton_em_ctx* ctx, const proton_em_batch* b,
   int64_t max_nodes = 0;
   for (const auto& ch : p0->chunks) max_nodes = std::max<int64_t>(max_nodes, p0->node_off[ch.l1] - p0->node_off[ch.l0]);
   const size_t field = (size_t)max_nodes * T;
-  CU_TRY(cudaDeviceSynchronize());
+  if (ctx->io_ts.n < (size_t)T * S || ctx->io_mx.n < LT || ctx->io_stress[0].n < field || ctx->io_stress[1].n < field ||
+      ctx->io_tmp.n < field) {
+    CU_TRY(cudaStreamSynchronize(ctx->stream));
+    CU_TRY(cudaStreamSynchronize(ctx->copy_stream));
+  }
   CU_TRY(grow(ctx->io_ts, (size_t)T * S)); CU_TRY(grow(ctx->io_mx, LT)); CU_TRY(grow(ctx->io_amx, LT)); CU_TRY(grow(ctx->io_flag, LT));
   CU_TRY(grow(ctx->io_stress[0], field)); CU_TRY(grow(ctx->io_stress[1], field)); CU_TRY(grow(ctx->io_tmp, field));
   cudaStream_t st = ctx->stream, cs = ctx->copy_stream;
@@ -1545,6 +1557,9 @@ extern "C" int proton_em_eval_line_noalloc(int device, void* stream_v, int32_t n
       (num_curden > 0 && !d_curden))
     return fail(PROTON_EM_EINVAL, "proton_em_eval_line_noalloc: NULL pointer argument");
   if (device < 0 || device >= kNoAllocMaxDevices) return fail(PROTON_EM_EINVAL, "device %d out of range", device);
+  // the caller's current device is put back on every way out
+  struct DeviceGuard { int prev = -1; ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); } } dguard;
+  if (cudaGetDevice(&dguard.prev) != cudaSuccess) dguard.prev = -1;
   CU_TRY(cudaSetDevice(device));
   if (!g_noalloc_ptr[device]) {
     // The array's name is only a host-side handle: ask the runtime where it lives on THIS device.
@@ -1554,8 +1569,9 @@ extern "C" int proton_em_eval_line_noalloc(int device, void* stream_v, int32_t n
   }
   NoAllocScratch* s = g_noalloc_ptr[device];
   cudaStream_t st = static_cast<cudaStream_t>(stream_v);
-  // lambda_k from the host libm (same reason as in ensure_tables); a fixed host buffer, no heap.
-  static double h_lam[kNoAllocMaxNodes];
+  // lambda_k from the host libm (same reason as in ensure_tables); a fixed per-thread host buffer, no heap, so host
+  // threads that serve different devices do not share it (the copy below is staged before cudaMemcpyAsync returns).
+  static thread_local double h_lam[kNoAllocMaxNodes];
   host_lambda(num_nodes, h_lam);
   CU_TRY(cudaMemcpyAsync(s->lam, h_lam, (size_t)num_nodes * sizeof(double), cudaMemcpyHostToDevice, st));
   em_noalloc_setup_kernel<<<1, 128, 0, st>>>(s, num_nodes, a_coeff, num_triplets, num_curden);
@@ -1568,7 +1584,7 @@ extern "C" int proton_em_eval_line_noalloc(int device, void* stream_v, int32_t n
                        s->trip_off, s->r_idx, s->r_val, s->r_cnt, s->line_tab, s->tab, s->W};
   em::em_forward_kernel<<<(fp.total_blocks + 127) / 128, 128, 0, st>>>(fp);
   CU_TRY(cudaGetLastError());
-  em::DirectParams dp{1, T, s->num_nodes, s->a_coeff, s->node_off, s->line_tab, s->tab, s->W, d_ts, s->exp_tab,
+  em::DirectParams dp{1, 0, T, s->num_nodes, s->a_coeff, s->node_off, s->line_tab, s->tab, s->W, d_ts, s->exp_tab,
                       d_stress, d_max_stress, d_argmax, d_flag, critical_stress};
   em::em_eval_direct_kernel<<<(unsigned)T, 256, 0, st>>>(dp);
   CU_TRY(cudaGetLastError());

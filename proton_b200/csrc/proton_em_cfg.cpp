@@ -2,7 +2,7 @@
 //
 // Mirrors main / simulation_engine::read_file / analyical_wrapper / tripletParser of the reference
 // binary (bin/EMtool_analytical@0x6920, @0xaaf4, @0xb93c, @0xb010), including
-// the texts it prints to stdout before exit(1) (captured by running the binary, tests/test_launcher.py).
+// the texts it prints to stdout before exit(1) (captured by running the binary, tests/test_launcher_cpu.py).
 // The arithmetic itself goes through proton_em_pack / proton_em_eval on the GPU.
 //
 // Deliberate differences (the reference aborts with SIGABRT in these cases; we report an error, rc 1):

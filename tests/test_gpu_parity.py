@@ -375,3 +375,48 @@ def test_batched_analyze_driver_and_launcher_class(ctx, oracle, ibmpg1_lines, tm
     want, _, _ = oracle.line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, [6.38e8])
     assert len(got) == li.num_nodes and np.abs(got - want[0]).max() <= 1e-9 * np.abs(want[0]).max()
     assert "No discretization" in Analytical_Class(1e6, str(proj), "nope", "CuDD", 378.0, 0.1, ctx=ctx).analytical_function()
+
+
+def test_direct_algorithm_respects_chunks_of_the_host_path(ctx):
+    """analyze_host splits the field into chunks; the DIRECT cross-check algorithm must write only the chunk it was
+    asked for (it once launched over every line of the batch and wrote outside the staging buffer)."""
+    from proton_b200.api import ALG_DIRECT
+    rng = np.random.default_rng(31)
+    batch = synth_batch(rng, [40, 300, 64, 700, 33, 500, 256, 120])
+    ts = np.array([1e6, 1e8, 6.38e8])
+    auto = ctx.analyze_host(batch, ts, critical=1e7)
+    small = 2 * (700 * 3 * 8 + 4096)            # two staging buffers of about one longest line each: >= 3 chunks
+    direct = ctx.analyze_host(batch, ts, critical=1e7, algorithm=ALG_DIRECT, max_device_bytes=small)
+    for l in range(batch.num_lines):
+        a, b = auto.line(l), direct.line(l)
+        assert np.abs(a - b).max() <= 1e-11 * np.abs(b).max(), l
+    assert np.allclose(auto.max_stress, direct.max_stress, rtol=1e-11, atol=0)
+    # and the pooled device buffers survived: the plain path still gives the same bits afterwards
+    again = ctx.analyze_host(batch, ts, critical=1e7)
+    assert np.array_equal(again.stress, auto.stress) and np.array_equal(again.argmax, auto.argmax)
+
+
+def test_line_length_limit_is_pinned(ctx, oracle):
+    """N = 65536 is the longest line of arbitrary length (131072 for powers of two); 65537 is rejected by name."""
+    from proton_b200.api import LineBatch, ProtonEmError
+    rng = np.random.default_rng(8)
+    ok = LineBatch.from_lines([synth_line(rng, 65535, 3)])
+    ts = np.array([1e7, 6.38e8])
+    got = ctx.analyze_host(ok, ts, critical=40e6)
+    ws, wm, wa = oracle_batch(oracle, ok, ts)
+    compare(ok, ts, got, ws, wm, wa, critical=40e6)
+    for n in (65537, 131073, 262144):
+        with pytest.raises(ProtonEmError, match=f"{n} nodes"):
+            ctx.pack(LineBatch.from_lines([synth_line(rng, n, 2)]))
+
+
+def test_context_closed_before_its_plans():
+    """Closing a context first closes the plans that point into it; a later Plan.close() is a no-op."""
+    from proton_b200.api import Context
+    rng = np.random.default_rng(4)
+    c = Context(0)
+    plan = c.pack(synth_batch(rng, [100, 5000]))
+    plan.eval(np.array([1e7]))
+    c.close()
+    plan.close()
+    del plan
