@@ -75,16 +75,26 @@ class LineBatch:
                          names=[getattr(li, "name", str(i)) for i, li in enumerate(lines)])
 
     def subset(self, idx: Sequence[int]) -> "LineBatch":
+        """The lines `idx` (any order, repeats allowed) as a batch of their own."""
         idx = np.asarray(idx, dtype=np.int64)
         tl = self.trip_off[idx + 1] - self.trip_off[idx]
         ul = self.u_off[idx + 1] - self.u_off[idx]
-        trip_off = np.concatenate([[0], np.cumsum(tl)])
-        u_off = np.concatenate([[0], np.cumsum(ul)])
-        tsel = np.concatenate([np.arange(self.trip_off[i], self.trip_off[i + 1]) for i in idx]) if len(idx) else np.zeros(0, np.int64)
-        usel = np.concatenate([np.arange(self.u_off[i], self.u_off[i + 1]) for i in idx]) if len(idx) else np.zeros(0, np.int64)
+        trip_off = np.concatenate([[0], np.cumsum(tl)]).astype(np.int64)
+        u_off = np.concatenate([[0], np.cumsum(ul)]).astype(np.int64)
+        # element e of the new triplet array comes from old position start_of_its_line + (e - new_start_of_its_line)
+        tsel = np.repeat(self.trip_off[idx] - trip_off[:-1], tl) + np.arange(int(trip_off[-1]), dtype=np.int64)
+        usel = np.repeat(self.u_off[idx] - u_off[:-1], ul) + np.arange(int(u_off[-1]), dtype=np.int64)
         return LineBatch(self.num_nodes[idx], self.a_coeff[idx], trip_off, self.trip_row[tsel], self.trip_col[tsel],
                          self.trip_val[tsel], u_off, self.curden[usel],
                          names=[self.names[i] for i in idx] if self.names else None)
+
+    def slice(self, l0: int, l1: int) -> "LineBatch":
+        """The contiguous lines [l0, l1) (views where possible)."""
+        t0, t1 = int(self.trip_off[l0]), int(self.trip_off[l1])
+        c0, c1 = int(self.u_off[l0]), int(self.u_off[l1])
+        return LineBatch(self.num_nodes[l0:l1], self.a_coeff[l0:l1], self.trip_off[l0:l1 + 1] - t0, self.trip_row[t0:t1],
+                         self.trip_col[t0:t1], self.trip_val[t0:t1], self.u_off[l0:l1 + 1] - c0, self.curden[c0:c1],
+                         names=self.names[l0:l1] if self.names else None)
 
     def _as_c(self) -> Batch:
         p = lambda a: a.ctypes.data if a.size else None

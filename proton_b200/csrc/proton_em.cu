@@ -380,6 +380,7 @@ inline size_t long_pair_smem(int p1) { return ((size_t)(p1 + 1) / 2 + 1) * 128 *
 
 int init_long_attrs() {
   CU_TRY(cudaFuncSetAttribute(em::em_long_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLongRowSmem));
+  CU_TRY(cudaFuncSetAttribute(em::em_long_row2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)em::kLongRow2Smem));
 #define M(q)                                                                                                              \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));        \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_paired_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_pair_smem(q)));
@@ -504,9 +505,28 @@ int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::L
   return PROTON_EM_OK;
 }
 
+// Row pass.  The Bluestein evaluation (mode 0) runs two rows per CTA with H staged in shared memory by a bulk copy
+// (em_long_row2_kernel; PROTON_EM_ROW2=0 selects the one-row kernel); table build and power-of-two lines use the one-row kernel.
+bool row2_enabled() {
+  static const bool v = [] { const char* e = std::getenv("PROTON_EM_ROW2"); return !(e && std::atoi(e) == 0); }();
+  return v;
+}
 int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp, int n_tr) {
-  const dim3 grid(rp.p1, n_tr);
   ProfScope prof(ctx, PK_LONG_ROW, st);
+  if (rp.mode == 0 && row2_enabled()) {
+    const dim3 grid2(rp.p1, (n_tr + 1) / 2);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid2; cfg.blockDim = dim3(em::kLongRow2Threads); cfg.dynamicSmemBytes = em::kLongRow2Smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    CU_TRY(cudaLaunchKernelEx(&cfg, em::em_long_row2_kernel, rp, n_tr));
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
+    return PROTON_EM_OK;
+  }
+  const dim3 grid(rp.p1, n_tr);
   CU_TRY(launch_pdl(em::em_long_row_kernel, grid, em::kLongRowThreads, kLongRowSmem, st, rp));
   ctx->launches++;
   CU_TRY(cudaGetLastError());
@@ -598,7 +618,7 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
       t.post = static_cast<const em::cplx*>(p);
-      const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2 : ((size_t)1 << c.log2p);
+      const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongRowPL : ((size_t)1 << c.log2p);
       CU_TRY(ctx->arena.alloc(&p, plen * sizeof(em::cplx)));
       t.hhat = static_cast<const em::cplx*>(p);
     }

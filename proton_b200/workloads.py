@@ -130,6 +130,24 @@ def synthetic_ragged(num_lines: int, seed: int = 0, nmin: int = 16, nmax: int = 
     return LineBatch(N.astype(np.int32), a, trip_off, rows, cols, vals, u_off, curden)
 
 
+def config4_batch(target_nodes: int = 10_000_000, seed: int = 4) -> LineBatch:
+    """BASELINE config 4: a 10 M-node power grid with the ibmpg length mix — the ibmpg2-shaped
+    population, and further seeded draws from it (with replacement) until the node count is reached."""
+    base = LineBatch.from_lines(ibmpg2_shaped_lines(replicas=7, seed=2))
+    rng = np.random.default_rng(seed)
+    nn = base.num_nodes.astype(np.int64)
+    extra = []
+    total = int(nn.sum())
+    while total < target_nodes:
+        i = int(rng.integers(0, base.num_lines))
+        if total + nn[i] > target_nodes + 30000:
+            continue
+        extra.append(i)
+        total += int(nn[i])
+    idx = np.concatenate([np.arange(base.num_lines), np.array(extra, dtype=np.int64)])
+    return base.subset(idx)
+
+
 def kernel_class(n: int, dense_max: int = 88) -> str:
     """Which kernel family evaluates a line of n nodes (mirror of classify() in csrc/proton_em.cu)."""
     pow2 = n & (n - 1) == 0

@@ -33,27 +33,42 @@ def _free_port():
 
 
 def _worker(rank, world, port, q):
+    """What bench.py does with N > 1, on CPU: every rank evaluates its shard (here: with the oracle), the three per-line
+    reductions are all-gathered, and rank 0 checks lines owned by the other rank against the oracle through the same
+    bench.check_gathered that runs on the GPUs."""
+    import sys
+    from pathlib import Path
     import torch
     import torch.distributed as dist
+    sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+    import bench
+    from oracle import restatement as R
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     batch = synthetic_ragged(200, seed=5, nmin=1, nmax=300)
     parts = partition_lines(batch.num_nodes, world)
-    mine = parts[rank]
-    T = 3
-    # stand-in for the per-line reductions of this rank's shard: a function of the global line id
-    local = torch.tensor(np.outer(mine + 1, np.arange(1, T + 1)).astype(np.float64))
+    mine = batch.subset(parts[rank])
+    ts = np.array([1e6, 5e7, 6.38e8])
+    T = len(ts)
+    _, mx, amx = R.batch(mine.num_nodes, mine.a_coeff, mine.trip_off, mine.trip_row, mine.trip_col, mine.trip_val,
+                         mine.u_off, mine.curden, ts, want_stress=False)
+    flag = (mx > bench.CRITICAL).astype(np.uint8)
     Lmax = max(len(p) for p in parts)
-    send = torch.zeros(Lmax * T, dtype=torch.float64)
-    send[: local.numel()] = local.reshape(-1)
-    recv = torch.empty(world * Lmax * T, dtype=torch.float64)
-    dist.all_gather_into_tensor(recv, send)
-    full = np.zeros((batch.num_lines, T))
-    for r in range(world):
-        blk = recv[r * Lmax * T:(r + 1) * Lmax * T].numpy().reshape(Lmax, T)
-        full[parts[r]] = blk[: len(parts[r])]
-    ok = np.array_equal(full, np.outer(np.arange(batch.num_lines) + 1, np.arange(1, T + 1)))
+    recv = []
+    for arr, dt in ((mx, torch.float64), (amx, torch.int32), (flag, torch.uint8)):
+        send = torch.zeros(Lmax * T, dtype=dt)
+        send[: arr.size] = torch.from_numpy(np.ascontiguousarray(arr)).reshape(-1)
+        out = torch.empty(world * Lmax * T, dtype=dt)
+        dist.all_gather_into_tensor(out, send)
+        recv.append(out.numpy())
+    ok = True
+    if rank == 0:
+        good = bench.check_gathered(batch, parts, ts, recv, Lmax, T, per_rank=5)
+        ok = good["ok"] and good["lines_checked"] == 5 * (world - 1)
+        # a shard -> line mapping that is off by one line must be caught
+        shifted = [np.roll(r.reshape(world, Lmax, T), 1, axis=1).reshape(-1) for r in recv]
+        ok = ok and not bench.check_gathered(batch, parts, ts, shifted, Lmax, T, per_rank=5)["ok"]
     q.put((rank, bool(ok)))
     dist.destroy_process_group()
 

@@ -40,7 +40,8 @@ def main():
         from proton_b200.workloads import synthetic_ragged
         batch, desc = None, {"T": args.T}
     else:
-        batch, desc = bench.build_workload(args.workload, 1, 0)
+        batch, T0 = bench.build_global(args.workload)
+        desc = {"T": T0}
     T = desc["T"]
     ts = bench.timestamps(T)
     dev = torch.device("cuda:0")
