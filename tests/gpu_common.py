@@ -43,13 +43,28 @@ def oracle_batch(oracle, batch: LineBatch, ts, want_stress=True):
                         batch.trip_val, batch.u_off, batch.curden, ts, want_stress=want_stress)
 
 
-def compare(batch: LineBatch, ts, got, want_stress, want_mx, want_amx, tol=1e-9, critical=None):
+class Escapes:
+    """How often a comparison with the oracle needed the near-tie escape: two different DCT algorithms cannot agree in
+    the last bit (SURVEY.md §7 hard part 2), so an arg-max may move between two nodes whose stresses differ by less
+    than the tolerance, and a flag may flip when the maximum sits within the tolerance of the threshold.  Every use of
+    the escape is counted here; the tests assert the counts against committed bounds (bit-exact agreement of max /
+    argmax / flag is asserted separately against the CPU twin of the GPU arithmetic, tests/test_twin.py)."""
+
+    def __init__(self):
+        self.rows = self.argmax = self.flag = 0
+
+    def __repr__(self):
+        return f"{self.argmax} arg-max and {self.flag} flag escapes in {self.rows} (line, t) rows"
+
+
+def compare(batch: LineBatch, ts, got, want_stress, want_mx, want_amx, tol=1e-9, critical=None, escapes: Escapes = None):
     """Norm-wise parity per (line, t): max|d| <= tol * max|sigma| (SURVEY.md §7 hard part 1-iii); max within
     tol; arg-max equal unless the runner-up is within tol of the maximum; flag equal unless the maximum sits
-    within tol of the threshold.  Returns the worst norm-wise error seen."""
+    within tol of the threshold (both escapes are counted in `escapes`).  Returns the worst norm-wise error seen."""
     T = len(ts)
     off = batch.node_off
     worst = 0.0
+    esc = escapes if escapes is not None else Escapes()
     for l in range(batch.num_lines):
         N = int(batch.num_nodes[l])
         g = got.stress[off[l] * T:off[l + 1] * T].reshape(T, N)
@@ -60,13 +75,14 @@ def compare(batch: LineBatch, ts, got, want_stress, want_mx, want_amx, tol=1e-9,
         assert ok.all(), f"line {l} (N={N}): norm-wise error {(err / np.maximum(scale, 1e-300)).max():.3e}"
         worst = max(worst, float((err / np.maximum(scale, 1e-300)).max()))
         assert np.all(np.abs(got.max_stress[l] - want_mx[l]) <= tol * scale + 1e-300)
-        for j in range(T):
-            if got.argmax[l, j] != want_amx[l, j]:
-                assert abs(w[j, got.argmax[l, j]] - w[j, want_amx[l, j]]) <= 2 * tol * scale[j], (l, j)
-            if critical is not None:
-                wf = want_mx[l, j] > critical
-                if bool(got.flag[l, j]) != wf:
-                    assert abs(want_mx[l, j] - critical) <= 2 * tol * scale[j], (l, j)
+        esc.rows += T
+        for j in np.nonzero(got.argmax[l] != want_amx[l])[0]:
+            esc.argmax += 1
+            assert abs(w[j, got.argmax[l, j]] - w[j, want_amx[l, j]]) <= 2 * tol * scale[j], (l, j)
+        if critical is not None:
+            for j in np.nonzero(got.flag[l].astype(bool) != (want_mx[l] > critical))[0]:
+                esc.flag += 1
+                assert abs(want_mx[l, j] - critical) <= 2 * tol * scale[j], (l, j)
     return worst
 
 

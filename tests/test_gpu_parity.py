@@ -4,11 +4,12 @@ states; N == 1 lines must be exact."""
 import numpy as np
 import pytest
 
-from gpu_common import compare, oracle_batch, self_consistent, synth_batch, synth_line
+from gpu_common import Escapes, compare, oracle_batch, self_consistent, synth_batch, synth_line
 
 pytestmark = pytest.mark.gpu
 
 TS100 = np.logspace(6, np.log10(6.38e8), 100)
+ESC = Escapes()      # near-tie escapes of every oracle comparison in this module (asserted by the last test)
 
 
 @pytest.fixture(scope="module")
@@ -100,7 +101,7 @@ def test_all_length_classes_against_oracle(ctx, oracle, T):
         ts = np.array([1e6, 3e6, 1e7, 5e7, 1e8, 3e8, 6.38e8])
     got = ctx.analyze_host(batch, ts, critical=40e6)
     ws, wm, wa = oracle_batch(oracle, batch, ts)
-    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6, escapes=ESC)
     self_consistent(batch, ts, got, 40e6)
     print(f"T={T}: worst norm-wise error {worst:.3e}")
 
@@ -113,7 +114,7 @@ def test_random_ragged_batch_against_oracle(ctx, oracle):
     plan = ctx.pack(batch)
     got = plan.eval(ts, critical=1e8)
     ws, wm, wa = oracle_batch(oracle, batch, ts)
-    compare(batch, ts, got, ws, wm, wa, critical=1e8)
+    compare(batch, ts, got, ws, wm, wa, critical=1e8, escapes=ESC)
     self_consistent(batch, ts, got, 1e8)
     # the plan can be evaluated again at other timestamps (and in reduce-only mode)
     got2 = plan.eval(ts[3:5], critical=1e8, want_stress=False)
@@ -134,7 +135,7 @@ def test_long_lines_against_oracle(ctx, oracle, T):
     ts = np.array([1e6, 2e7, 6.38e8, 1e8])[:T]
     got = ctx.analyze_host(batch, ts, critical=40e6)
     ws, wm, wa = oracle_batch(oracle, batch, ts)
-    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6, escapes=ESC)
     self_consistent(batch, ts, got, 40e6)
     print(f"long lines T={T}: worst norm-wise error {worst:.3e}")
 
@@ -148,7 +149,7 @@ def test_ibmpg1_full_grid_against_oracle(ctx, oracle):
     ts = np.array([1e6, 1e7, 6.38e8])
     got = ctx.analyze_host(batch, ts, critical=40e6)
     ws, wm, wa = oracle_batch(oracle, batch, ts)
-    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6, escapes=ESC)
     self_consistent(batch, ts, got, 40e6)
     print(f"ibmpg1 full grid: worst norm-wise error {worst:.3e}; flagged lines {int(got.flag[:, -1].sum())}")
 
@@ -236,7 +237,7 @@ def test_current_history_against_oracle_superposition(ctx, oracle):
     got = ctx.analyze_history(batch, segs, seg_start, ts, critical=40e6)
     ws, wm, wa = oracle.history_batch(batch.num_nodes, batch.a_coeff, batch.trip_off, batch.trip_row, batch.trip_col,
                                       batch.trip_val, batch.u_off, segs, seg_start, ts)
-    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6)
+    worst = compare(batch, ts, got, ws, wm, wa, critical=40e6, escapes=ESC)
     self_consistent(batch, ts, got, 40e6)
     print(f"history: worst norm-wise error {worst:.3e}")
     # one segment is exactly the plain evaluation; repeating the same current changes nothing
@@ -404,7 +405,7 @@ def test_line_length_limit_is_pinned(ctx, oracle):
     ts = np.array([1e7, 6.38e8])
     got = ctx.analyze_host(ok, ts, critical=40e6)
     ws, wm, wa = oracle_batch(oracle, ok, ts)
-    compare(ok, ts, got, ws, wm, wa, critical=40e6)
+    compare(ok, ts, got, ws, wm, wa, critical=40e6, escapes=ESC)
     for n in (65537, 131073, 262144):
         with pytest.raises(ProtonEmError, match=f"{n} nodes"):
             ctx.pack(LineBatch.from_lines([synth_line(rng, n, 2)]))
@@ -420,3 +421,14 @@ def test_context_closed_before_its_plans():
     c.close()
     plan.close()
     del plan
+
+
+def test_zz_near_tie_escapes_stay_within_the_committed_bounds():
+    """The comparisons above accept an arg-max / flag difference only when the oracle's own field shows a tie within
+    2e-9 of the scale.  This counts how often that happened in the whole module: it has to stay a rare event (bounds
+    committed from the B200 runs of this round; the bit-exact statement lives in tests/test_twin.py)."""
+    print(f"oracle comparisons of this module: {ESC}")
+    if ESC.rows == 0:
+        pytest.skip("no oracle comparison ran before this test")
+    assert ESC.argmax <= max(2, 2e-3 * ESC.rows), ESC
+    assert ESC.flag <= max(1, 2e-4 * ESC.rows), ESC
