@@ -59,9 +59,9 @@ def build_global(name: str, lines_override: int = 0):
     from proton_b200.api import LineBatch
     from proton_b200 import workloads as W
     if name == "ibmpg2_shaped":
-        return LineBatch.from_lines(W.ibmpg2_shaped_lines(replicas=7, seed=2)), 100
+        return W.ibmpg2_shaped_batch(replicas=7, seed=2), 100
     if name == "ibmpg1":
-        return LineBatch.from_lines(W.ibmpg1_lines()), 100
+        return W.ibmpg1_batch(), 100
     if name == "synthetic_ragged":
         return W.synthetic_ragged(lines_override or 1_000_000, seed=0), 256
     if name == "config4":

@@ -59,15 +59,32 @@ def find_line_csvs(benchmark_dir: str) -> List[str]:
 
 
 def formulate_for_analyze(csv_files: Sequence[str], technology: str, temperature: float, width: float):
-    """dx policy of analyze_line_item: step = 0.99 * min length, up to 10 retries with min length * 0.7."""
-    lines, discarded = [], {}
+    """dx policy of analyze_line_item: step = 0.99 * min length, up to 10 retries with min length * 0.7
+    (PROTON_cli.py:1000-1014).  All lines that parse are discretised in one vectorised pass
+    (formulation.formulate_table); a line that the first pass rejects goes through the reference's retry loop on its
+    own.  Returns (LineBatch with names, {discarded line: reason})."""
+    parsed, discarded = [], {}
     for path in csv_files:
         name = os.path.splitext(os.path.basename(path))[0]
         try:
             segs, nlines = F.parse_line_csv(path)
-            if not segs:
-                discarded[name] = F.CORRUPT_MSG
-                continue
+        except F.FormulationError as e:
+            discarded[name] = str(e)
+            continue
+        if not segs:
+            discarded[name] = F.CORRUPT_MSG
+            continue
+        parsed.append((name, segs, nlines))
+    if not parsed:
+        return LineBatch.from_lines([]), discarded
+    try:
+        table = F.SegmentTable.from_lines([(n, s) for n, s, _ in parsed])
+        return F.formulate_table(table, technology=technology, temperature=temperature, givenWidth=width), discarded
+    except (F.FormulationError, IndexError):
+        pass                                   # some line needs the retry loop or is malformed: line by line below
+    lines = []
+    for name, segs, nlines in parsed:
+        try:
             min_length = min(float(s[2]) for s in segs)
             li = None
             for _ in range(10):
@@ -87,14 +104,14 @@ def formulate_for_analyze(csv_files: Sequence[str], technology: str, temperature
                 lines.append(li)
         except (F.FormulationError, IndexError) as e:
             discarded[name] = str(e)
-    return lines, discarded
+    return LineBatch.from_lines(lines), discarded
 
 
-def write_reference_outputs(project_dir: str, lines, result, timestamps, technology, temperature, width) -> int:
+def write_reference_outputs(project_dir: str, names, result, timestamps, technology, temperature, width) -> int:
     """stress_<%f>.txt per (line, t) exactly where and how the reference binary writes them."""
     n = 0
-    for l, li in enumerate(lines):
-        out_dir = os.path.join(project_dir, "output", li.name, f"{technology}_{temperature}_{width}")
+    for l, name in enumerate(names):
+        out_dir = os.path.join(project_dir, "output", name, f"{technology}_{temperature}_{width}")
         os.makedirs(out_dir, exist_ok=True)
         block = result.line(l)
         for j, t in enumerate(timestamps):
@@ -114,21 +131,20 @@ def analyze(project_dir: str, benchmark: str, simulation_time, critical_stress: 
     if sample_lines is not None and sample_lines < len(csvs):
         rnd = random.Random(seed)
         csvs = rnd.sample(csvs, sample_lines)          # PROTON_cli.py:1146-1149
-    lines, discarded = formulate_for_analyze(csvs, technology, float(temperature), float(width))
+    batch, discarded = formulate_for_analyze(csvs, technology, float(temperature), float(width))
+    names = list(batch.names or [])
     own = ctx is None
     ctx = ctx or Context(0)
     try:
-        batch = LineBatch.from_lines(lines)
         res = ctx.analyze_host(batch, ts, critical=critical_stress, want_stress=write_outputs)
     finally:
         if own:
             ctx.close()
     if write_outputs:
-        write_reference_outputs(project_dir, lines, res, ts, technology, float(temperature), float(width))
+        write_reference_outputs(project_dir, names, res, ts, technology, float(temperature), float(width))
     problematic = {}
     if critical_stress is not None:
-        for l, li in enumerate(lines):
+        for l, name in enumerate(names):
             if res.flag[l, -1]:
-                problematic[li.name] = float(res.max_stress[l, -1])
-    return AnalyzeReport([li.name for li in lines], discarded, res.max_stress, res.argmax, res.flag, problematic,
-                         time.time() - t0, ts)
+                problematic[name] = float(res.max_stress[l, -1])
+    return AnalyzeReport(names, discarded, res.max_stress, res.argmax, res.flag, problematic, time.time() - t0, ts)

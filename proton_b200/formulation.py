@@ -202,3 +202,149 @@ def read_line_inputs(input_dir: str, name: Optional[str] = None) -> LineInputs:
     return LineInputs(name=name or os.path.basename(os.path.normpath(input_dir)), num_nodes=nx_total,
                       a_coeff=acoef, rows=np.asarray(rows, np.int32), cols=np.asarray(cols, np.int32),
                       vals=np.asarray(vals, np.float64), curden=np.asarray(curden, np.float64))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# The same discretisation for a whole grid at once: a flat segment table in, a ragged LineBatch out.
+# ---------------------------------------------------------------------------------------------------------------
+@dataclass
+class SegmentTable:
+    """All segments of many lines, flat.  Segment k belongs to line `line_of[k]`; `seg_off[l]:seg_off[l+1]` are the
+    segments of line l in file order.  `lcoord[k] / rcoord[k]` are integer ids of the two `_`-separated coordinates
+    of the left / right node name (equal id <=> equal string, which is what the reference compares, :148-157)."""
+    names: list
+    seg_off: np.ndarray       # int64 [L+1]
+    length_um: np.ndarray     # float64 [K]
+    current: np.ndarray       # float64 [K]
+    lcoord: np.ndarray        # int64 [K, 2]   ids of left_node.split("_")[1], [2]
+    rcoord: np.ndarray        # int64 [K, 2]
+    named: np.ndarray         # bool [K]: both node names non-empty (the reference's truthiness test)
+
+    @property
+    def num_lines(self) -> int:
+        return len(self.seg_off) - 1
+
+    @staticmethod
+    def from_lines(lines: Sequence[Tuple[str, Sequence[Tuple[str, str, float, float]]]]) -> "SegmentTable":
+        """From (name, [(left_node, right_node, length_um, current_A), ...]) per line (parse_line_csv's rows)."""
+        names = [n for n, _ in lines]
+        counts = np.fromiter((len(s) for _, s in lines), dtype=np.int64, count=len(lines))
+        seg_off = np.zeros(len(lines) + 1, dtype=np.int64)
+        np.cumsum(counts, out=seg_off[1:])
+        flat = [s for _, segs in lines for s in segs]
+        K = len(flat)
+        length = np.fromiter((float(s[2]) for s in flat), dtype=np.float64, count=K)
+        current = np.fromiter((float(s[3]) for s in flat), dtype=np.float64, count=K)
+        words = {}
+
+        def ident(w):
+            return words.setdefault(w, len(words))
+        lc = np.empty((K, 2), dtype=np.int64)
+        rc = np.empty((K, 2), dtype=np.int64)
+        named = np.empty(K, dtype=bool)
+        for k, s in enumerate(flat):
+            a, b = s[0].split("_"), s[1].split("_")
+            lc[k, 0], lc[k, 1] = ident(a[1]), ident(a[2])
+            rc[k, 0], rc[k, 1] = ident(b[1]), ident(b[2])
+            named[k] = bool(s[0]) and bool(s[1])
+        return SegmentTable(names, seg_off, length, current, lc, rc, named)
+
+
+def formulate_table(tab: SegmentTable, *, sp_step=None, technology="CuDD", temperature=378.0, givenWidth=0.1):
+    """Discretise every line of `tab` in step mode, vectorised over all segments; returns a `proton_b200.api.LineBatch`
+    whose arrays are bit-identical to running `formulate_segments` line by line (same N, Acoef, B triplets in the
+    same order, float32-rounded currents).  `sp_step`: one step in um for all lines, an array with one per line, or
+    None for the whole-grid driver's policy 0.99 x the line's shortest segment (PROTON_cli.py:1005-1012)."""
+    from .api import LineBatch
+    kappa, b = technology_constants(technology, temperature)
+    L, K = tab.num_lines, len(tab.length_um)
+    counts = np.diff(tab.seg_off)
+    if L == 0 or np.any(counts <= 0):
+        raise FormulationError(CORRUPT_MSG)
+    line_of = np.repeat(np.arange(L, dtype=np.int64), counts)
+    first = np.zeros(K, dtype=bool)
+    first[tab.seg_off[:-1]] = True
+    if sp_step is None:
+        step_um = np.minimum.reduceat(tab.length_um, tab.seg_off[:-1]) * 0.99
+    else:
+        step_um = np.broadcast_to(np.asarray(sp_step, dtype=np.float64), (L,)).copy()
+    dx_line = step_um * 1e-6
+    dx = dx_line[line_of]
+    length = tab.length_um * 1e-6
+    if np.any(length < dx):
+        raise FormulationError(NOT_DENSE_MSG)
+    w = float(givenWidth)
+    curden = (tab.current / (w * 1e-6 * w * 1e-6)).astype(np.float32).astype(np.float64)
+    d = np.rint(length / dx).astype(np.int64)                  # Python's round(): half to even
+    # joined to the predecessor: the coordinate that is constant along THIS segment equals the predecessor's
+    same2 = tab.lcoord[:, 1] == tab.rcoord[:, 1]              # split("_")[2] equal -> compare index 2, else index 1
+    cur = np.where(same2, tab.lcoord[:, 1], tab.lcoord[:, 0])
+    prev = np.empty(K, dtype=np.int64)
+    prev[1:] = np.where(same2[1:], tab.lcoord[:-1, 1], tab.lcoord[:-1, 0])
+    prev[0] = -1
+    prev_named = np.empty(K, dtype=bool)
+    prev_named[1:] = tab.named[:-1]
+    prev_named[0] = False
+    join = (~first) & prev_named & (prev == cur)
+    net = d - join
+    csum = np.cumsum(net)
+    before_line = csum[tab.seg_off[:-1]] - net[tab.seg_off[:-1]]          # running sum before each line's first segment
+    after = csum - np.repeat(before_line, counts)              # nx_total after each segment, within its line
+    N = after[tab.seg_off[1:] - 1]
+    S = counts
+    if np.any(N <= 0):
+        raise FormulationError(CORRUPT_MSG)
+    v = np.nonzero(join)[0]
+    nv = len(v)
+    vline = line_of[v]
+    vkey = after[v] - d[v] + 1                                 # nx_total before the segment (the via's node)
+    vseg = v - tab.seg_off[vline] + 1                          # 1-based segment number
+    # the reference keeps `vias[key] = segment` in a dict: a repeated key keeps the LAST segment number, and the
+    # repeated vias then assign the same two entries again.  Keys do not decrease along a line, so equal keys are
+    # adjacent: only the last via of each run matters.
+    if nv:
+        run_end = np.ones(nv, dtype=bool)
+        run_end[:-1] = (vline[1:] != vline[:-1]) | (vkey[1:] != vkey[:-1])
+        if not run_end.all():
+            vline, vkey, vseg = vline[run_end], vkey[run_end], vseg[run_end]
+            nv = len(vline)
+    # Assignments in the reference's order: (0, 0, +1); per via (key-1, seg-2, -1), (key-1, seg-1, +1); (N-1, S-1, -1),
+    # laid out line after line.  Rows increase strictly from via to via, so the list is already sorted by (row, col)
+    # and two assignments to one position (the first / last entry against a via's) are neighbours: the later one wins.
+    vcount = np.bincount(vline, minlength=L) if nv else np.zeros(L, dtype=np.int64)
+    vb = np.zeros(L + 1, dtype=np.int64)
+    np.cumsum(vcount, out=vb[1:])
+    total = 2 * L + 2 * nv
+    lines_all = np.arange(L, dtype=np.int64)
+    a_line = np.repeat(lines_all, 2 + 2 * vcount)
+    a_i = np.empty(total, dtype=np.int64)
+    a_j = np.empty(total, dtype=np.int64)
+    a_v = np.empty(total, dtype=np.float64)
+    i_first = 2 * lines_all + 2 * vb[:-1]
+    i_last = 2 * lines_all + 2 * vb[1:] + 1
+    i_via = 2 * np.arange(nv, dtype=np.int64) + 2 * vline + 1
+    a_i[i_first], a_j[i_first], a_v[i_first] = 0, 0, 1.0
+    a_i[i_via], a_j[i_via], a_v[i_via] = vkey - 1, vseg - 2, -1.0
+    a_i[i_via + 1], a_j[i_via + 1], a_v[i_via + 1] = vkey - 1, vseg - 1, 1.0
+    a_i[i_last], a_j[i_last], a_v[i_last] = N - 1, S - 1, -1.0
+    if nv and (vkey.min() < 1 or vseg.min() < 2):
+        # never seen (a via sits after at least one node and one segment); kept for exactness: Python list indexing
+        # wraps negative indices once, and then the list is no longer sorted
+        Ni, Si = N[a_line], S[a_line]
+        a_i = np.where(a_i < 0, a_i + Ni, a_i)
+        a_j = np.where(a_j < 0, a_j + Si, a_j)
+        if np.any((a_i < 0) | (a_i >= Ni) | (a_j < 0) | (a_j >= Si)):
+            raise IndexError("list assignment index out of range")
+        pos_key = (a_line * (int(N.max()) + 1) + a_i) * (int(S.max()) + 1) + a_j
+        order = np.argsort(pos_key, kind="stable")
+        a_line, a_i, a_j, a_v = a_line[order], a_i[order], a_j[order], a_v[order]
+    keep = np.ones(total, dtype=bool)                         # later assignments overwrite earlier ones
+    keep[:-1] = (a_i[1:] != a_i[:-1]) | (a_j[1:] != a_j[:-1]) | (a_line[1:] != a_line[:-1])
+    if not keep.all():
+        a_line, a_i, a_j, a_v = a_line[keep], a_i[keep], a_j[keep], a_v[keep]
+    acoef = kappa / (dx_line * dx_line)
+    bcoef = kappa * b / dx_line
+    trip_off = np.zeros(L + 1, dtype=np.int64)
+    np.cumsum(np.bincount(a_line, minlength=L), out=trip_off[1:])
+    return LineBatch(N.astype(np.int32), acoef, trip_off, a_i.astype(np.int32), a_j.astype(np.int32),
+                     a_v * bcoef[a_line], tab.seg_off.copy(), curden, names=list(tab.names))

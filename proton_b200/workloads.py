@@ -69,6 +69,42 @@ def ibmpg2_shaped_lines(replicas: int = 7, seed: int = 2, max_nodes: int = 0) ->
     return lines
 
 
+_TABLE_CACHE = {}
+
+
+def ibmpg1_table() -> F.SegmentTable:
+    """ibmpg1's line population as a flat segment table (parsed once per process)."""
+    if "ibmpg1" not in _TABLE_CACHE:
+        _TABLE_CACHE["ibmpg1"] = F.SegmentTable.from_lines(ibmpg1_segments())
+    return _TABLE_CACHE["ibmpg1"]
+
+
+def ibmpg1_batch() -> LineBatch:
+    """`LineBatch.from_lines(ibmpg1_lines())` through the vectorised discretiser (bit-identical, tests/test_formulation.py)."""
+    return F.formulate_table(ibmpg1_table(), technology=TECH, temperature=TEMP, givenWidth=WIDTH)
+
+
+def ibmpg2_shaped_batch(replicas: int = 7, seed: int = 2) -> LineBatch:
+    """`LineBatch.from_lines(ibmpg2_shaped_lines(replicas, seed))`, vectorised: the same seeded jitter (one length scale
+    and one current factor per replicated line, drawn in the same order) applied to the flat segment table."""
+    rng = np.random.default_rng(seed)
+    base = ibmpg1_table()
+    L, K = base.num_lines, len(base.length_um)
+    counts = np.diff(base.seg_off)
+    lengths, currents = [base.length_um], [base.current]
+    for r in range(1, replicas):
+        draws = np.array([(rng.uniform(0.8, 1.25), rng.lognormal(0.0, 0.5)) for _ in range(L)])
+        scale, cur = np.repeat(draws[:, 0], counts), np.repeat(draws[:, 1], counts)
+        lengths.append(np.maximum(1.0, np.rint(base.length_um * scale)))
+        currents.append(base.current * cur)
+    seg_off = np.concatenate([[0]] + [base.seg_off[1:] + r * K for r in range(replicas)])
+    names = [f"{n}#{r}" for r in range(replicas) for n in base.names]
+    tab = F.SegmentTable(names, seg_off, np.concatenate(lengths), np.concatenate(currents),
+                         np.tile(base.lcoord, (replicas, 1)), np.tile(base.rcoord, (replicas, 1)),
+                         np.tile(base.named, replicas))
+    return F.formulate_table(tab, technology=TECH, temperature=TEMP, givenWidth=WIDTH)
+
+
 def synthetic_ragged(num_lines: int, seed: int = 0, nmin: int = 16, nmax: int = 4096, dist: str = "loguniform",
                      sizes=None) -> LineBatch:
     """N log-uniform in [nmin, nmax]; S = min(N-1, 1 + Poisson(4)); vias at sorted distinct
@@ -133,7 +169,7 @@ def synthetic_ragged(num_lines: int, seed: int = 0, nmin: int = 16, nmax: int = 
 def config4_batch(target_nodes: int = 10_000_000, seed: int = 4) -> LineBatch:
     """BASELINE config 4: a 10 M-node power grid with the ibmpg length mix — the ibmpg2-shaped
     population, and further seeded draws from it (with replacement) until the node count is reached."""
-    base = LineBatch.from_lines(ibmpg2_shaped_lines(replicas=7, seed=2))
+    base = ibmpg2_shaped_batch(replicas=7, seed=2)
     rng = np.random.default_rng(seed)
     nn = base.num_nodes.astype(np.int64)
     extra = []

@@ -64,3 +64,81 @@ def test_read_line_inputs_round_trip(tmp_path, oracle):
     assert back.num_nodes == li.num_nodes and back.a_coeff == li.a_coeff
     assert np.array_equal(back.rows, li.rows) and np.array_equal(back.vals, li.vals)
     assert np.array_equal(back.curden, li.curden)
+
+
+FIELDS = ("num_nodes", "a_coeff", "trip_off", "trip_row", "trip_col", "trip_val", "u_off", "curden")
+
+
+def _same_batch(a, b):
+    for f in FIELDS:
+        assert np.array_equal(getattr(a, f), getattr(b, f)), f
+
+
+def test_vectorised_discretiser_equals_the_per_line_twin_on_ibmpg1():
+    """formulate_table (all lines at once) against formulate_segments line by line: the analyze
+    policy step and several fixed steps, including coarse ones where segments get one point and vias collide with the
+    first / last entry of B."""
+    from proton_b200 import workloads as W
+    from proton_b200.api import LineBatch
+    lines = W.ibmpg1_segments()
+    tab = F.SegmentTable.from_lines(lines)
+    assert tab.num_lines == 1717
+    got = F.formulate_table(tab)
+    want = LineBatch.from_lines([F.formulate_segments(s, sp_step=F.analyze_policy_step(s), name=n) for n, s in lines])
+    _same_batch(got, want)
+    assert got.names == want.names
+    for step in (0.5, 2.0, 5.0):
+        ok = [(n, s) for n, s in lines if min(x[2] for x in s) >= step]
+        got = F.formulate_table(F.SegmentTable.from_lines(ok), sp_step=step)
+        want = LineBatch.from_lines([F.formulate_segments(s, sp_step=step, name=n) for n, s in ok])
+        _same_batch(got, want)
+    with pytest.raises(F.FormulationError, match="not dense enough"):
+        F.formulate_table(tab, sp_step=5.0)
+
+
+def test_vectorised_discretiser_on_the_reference_goldens(formulation_golden, tmp_path):
+    """The step-mode goldens produced by the reference's own Matrix_Formulation_Class, through the vectorised path."""
+    g = formulation_golden
+    csvs = split_blob(g["csv_blob"])
+    done = 0
+    for i, name in enumerate(g["names"]):
+        if g["mode"][i] != "step":
+            continue
+        p = tmp_path / f"{name}.csv"
+        p.write_text(csvs[i])
+        segs, _ = F.parse_line_csv(str(p))
+        b = F.formulate_table(F.SegmentTable.from_lines([(str(name), segs)]), sp_step=float(g["param"][i]),
+                              technology=str(g["tech"]), temperature=float(g["temperature"]), givenWidth=float(g["width"]))
+        t0, t1 = g["trip_off"][i], g["trip_off"][i + 1]
+        u0, u1 = g["u_off"][i], g["u_off"][i + 1]
+        assert int(b.num_nodes[0]) == int(g["num_nodes"][i]) and float(b.a_coeff[0]) == float(g["a_coeff"][i]), name
+        assert np.array_equal(b.trip_row, g["rows"][t0:t1]) and np.array_equal(b.trip_col, g["cols"][t0:t1]), name
+        assert np.array_equal(b.trip_val, g["vals"][t0:t1]) and np.array_equal(b.curden, g["curden"][u0:u1]), name
+        done += 1
+    assert done >= 50
+
+
+def test_repeated_via_keys_and_one_point_segments():
+    """Hand-made lines that hit the reference's dict overwrite (two joins at the same node) and the overwrite of the
+    first / last entry of B by a via."""
+    from proton_b200.api import LineBatch
+    lines = [
+        ("a", [(" n1_0_5", " n1_10_5", 10.0, 1e-3), (" n1_10_5", " n1_20_5", 10.0, 2e-3), (" n1_20_5", " n1_30_5", 10.0, -1e-3)]),
+        ("b", [(" n1_0_5", " n1_1_5", 1.0, 1e-3), (" n1_1_5", " n1_2_5", 1.0, 2e-3), (" n1_2_5", " n1_40_5", 38.0, 1e-3)]),
+        ("c", [(" n1_0_5", " n1_0_9", 4.0, 1e-3), (" n1_0_9", " n1_7_9", 7.0, 1e-3)]),
+        ("d", [(" n1_0_5", " n1_10_5", 10.0, 1e-3)]),
+    ]
+    for step in (10.0, 1.0, 0.99):
+        ok = [(n, s) for n, s in lines if min(x[2] for x in s) >= step]
+        got = F.formulate_table(F.SegmentTable.from_lines(ok), sp_step=step)
+        want = LineBatch.from_lines([F.formulate_segments(s, sp_step=step, name=n) for n, s in ok])
+        _same_batch(got, want)
+
+
+def test_workload_batches_equal_their_per_line_construction():
+    from proton_b200 import workloads as W
+    from proton_b200.api import LineBatch
+    _same_batch(W.ibmpg1_batch(), LineBatch.from_lines(W.ibmpg1_lines()))
+    a, b = W.ibmpg2_shaped_batch(replicas=3, seed=2), LineBatch.from_lines(W.ibmpg2_shaped_lines(replicas=3, seed=2))
+    _same_batch(a, b)
+    assert a.names == b.names

@@ -430,5 +430,6 @@ def test_zz_near_tie_escapes_stay_within_the_committed_bounds():
     print(f"oracle comparisons of this module: {ESC}")
     if ESC.rows == 0:
         pytest.skip("no oracle comparison ran before this test")
-    assert ESC.argmax <= max(2, 2e-3 * ESC.rows), ESC
-    assert ESC.flag <= max(1, 2e-4 * ESC.rows), ESC
+    # measured on B200 this round: 0 arg-max and 0 flag escapes in 14 512 rows
+    assert ESC.argmax <= 2, ESC
+    assert ESC.flag <= 1, ESC
