@@ -346,6 +346,35 @@ class Shard:
         self.plans = []
 
 
+class Gather:
+    """The one exchange of the path: every rank contributes max (f64), argmax (i32) and flag (u8) of its lines at all
+    timestamps, packed into one byte buffer of 13 bytes per (line, t) (padded to the longest shard), and ONE NCCL
+    all-gather moves them; queued on the library's stream right behind the evaluation."""
+
+    def __init__(self, torch, dist, dev, stream, Lmax, T, world):
+        self.torch, self.dist, self.stream = torch, dist, stream
+        self.n, self.world = Lmax * T, world
+        self.send = torch.zeros(self.n * 13, dtype=torch.uint8, device=dev)
+        self.recv = torch.empty(world * self.n * 13, dtype=torch.uint8, device=dev)
+        n = self.n
+        self.views = (self.send[: 8 * n].view(torch.float64), self.send[8 * n: 12 * n].view(torch.int32), self.send[12 * n:])
+
+    def run(self, shard):
+        k = shard.L * shard.T
+        with self.torch.cuda.stream(self.stream):
+            for view, src in zip(self.views, (shard.d_mx, shard.d_amx, shard.d_flag)):
+                view[:k].copy_(src)
+            self.dist.all_gather_into_tensor(self.recv, self.send)
+
+    def unpack(self):
+        """-> [max (world*n f64), argmax (world*n i32), flag (world*n u8)] as numpy, rank-major."""
+        n = self.n
+        raw = self.recv.cpu().numpy().reshape(self.world, 13 * n)
+        return [np.ascontiguousarray(raw[:, : 8 * n]).view(np.float64).reshape(-1),
+                np.ascontiguousarray(raw[:, 8 * n: 12 * n]).view(np.int32).reshape(-1),
+                np.ascontiguousarray(raw[:, 12 * n:]).reshape(-1)]
+
+
 def time_steps(torch, stream, step, n, barrier):
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -440,14 +469,10 @@ def main():
     # ---- the only exchange of the path: all-gather of {max, argmax, flag} per (line, t) -----------------------------
     Lmax = max(len(p) for p in parts)
     if world > 1:
-        g_send = [torch.zeros(Lmax * T, dtype=dt, device=dev) for dt in (torch.float64, torch.int32, torch.uint8)]
-        g_recv = [torch.empty(world * Lmax * T, dtype=dt, device=dev) for dt in (torch.float64, torch.int32, torch.uint8)]
+        gth = Gather(torch, dist, dev, stream, Lmax, T, world)
 
     def gather():
-        with torch.cuda.stream(stream):
-            for snd, rcv, src in zip(g_send, g_recv, (shard.d_mx, shard.d_amx, shard.d_flag)):
-                snd[: L * T].copy_(src)
-                dist.all_gather_into_tensor(rcv, snd)
+        gth.run(shard)
 
     def step():
         shard.eval()
@@ -484,7 +509,7 @@ def main():
         # rank 0 checks the gathered reductions of lines owned by OTHER ranks against the CPU oracle
         barrier()
         if rank == 0:
-            multi["gather_check"] = check_gathered(gbatch, parts, ts, [t.cpu().numpy() for t in g_recv], Lmax, T)
+            multi["gather_check"] = check_gathered(gbatch, parts, ts, gth.unpack(), Lmax, T)
 
     # ---- roofline (this rank's share) ----------------------------------------------------------------------------
     roofline = build_roofline(args, ctx, shard, batch, T, ms_rank, barrier, W)
@@ -760,14 +785,10 @@ def run_config4(args, ctx, torch, dist, dev, stream, W, world, rank, barrier, al
     sh = Shard(ctx, torch, dev, mine, T)
     sh.pack()
     Lmax = max(len(p) for p in parts)
-    g_send = [torch.zeros(Lmax * T, dtype=dt, device=dev) for dt in (torch.float64, torch.int32, torch.uint8)]
-    g_recv = [torch.empty(world * Lmax * T, dtype=dt, device=dev) for dt in (torch.float64, torch.int32, torch.uint8)]
+    gth = Gather(torch, dist, dev, stream, Lmax, T, world)
 
     def gather():
-        with torch.cuda.stream(stream):
-            for snd, rcv, src in zip(g_send, g_recv, (sh.d_mx, sh.d_amx, sh.d_flag)):
-                snd[: sh.L * T].copy_(src)
-                dist.all_gather_into_tensor(rcv, snd)
+        gth.run(sh)
 
     def step():
         sh.eval()
@@ -791,9 +812,9 @@ def run_config4(args, ctx, torch, dist, dev, stream, W, world, rank, barrier, al
         prof = {k: v for k, v in ctx.profile_read().items() if v[1] > 0}
         prof_kernels = {k: {"ms_per_step": v[0], "launches_per_step": v[1]} for k, v in prof.items()}
     barrier()
-    check = check_gathered(gb, parts, timestamps(T), [t.cpu().numpy() for t in g_recv], Lmax, T, per_rank=2) if rank == 0 else None
+    check = check_gathered(gb, parts, timestamps(T), gth.unpack(), Lmax, T, per_rank=2) if rank == 0 else None
     sh.close()
-    del sh, g_send, g_recv
+    del sh, gth
     torch.cuda.empty_cache()
     # the whole batch on one GPU (every rank does it on its own GPU; they do not interact)
     whole = Shard(ctx, torch, dev, gb, T)

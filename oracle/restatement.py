@@ -238,3 +238,37 @@ def reference_binary_line(N, a, rows, cols, vals, u, t, workdir=None, fft: str =
     finally:
         if ctx:
             ctx.cleanup()
+
+
+# ---- CPU twin of the GPU arithmetic (oracle/em_twin.c) -----------------------------------------------------------
+TWIN_PATH = HERE / "libtwin.so"
+_twin = None
+
+
+def load_twin() -> ctypes.CDLL:
+    global _twin
+    if _twin is None:
+        if not TWIN_PATH.exists():
+            build()
+        lib = ctypes.CDLL(str(TWIN_PATH))
+        c_dp = ctypes.POINTER(ctypes.c_double)
+        for f in (lib.em_twin_dense, lib.em_twin_pow2):
+            f.argtypes = [ctypes.c_int, ctypes.c_double, c_dp, c_dp, c_dp, ctypes.c_int, c_dp, c_dp]
+            f.restype = ctypes.c_int
+        _twin = lib
+    return _twin
+
+
+def twin_line(kind: str, N: int, a: float, lam, W, table, ts) -> np.ndarray:
+    """Stress [T, N] of one line exactly as the GPU kernel of `kind` ("dense" | "pow2") computes it, given the device's
+    own tables: lambda, W, and `table` = the cosine table (dense) or the pre-twiddles (pow2)."""
+    lam = np.ascontiguousarray(lam, dtype=np.float64)
+    W = np.ascontiguousarray(W, dtype=np.float64)
+    table = np.ascontiguousarray(table, dtype=np.float64)
+    ts = np.ascontiguousarray(np.atleast_1d(ts), dtype=np.float64)
+    out = np.empty((len(ts), N), dtype=np.float64)
+    fn = load_twin().em_twin_dense if kind == "dense" else load_twin().em_twin_pow2
+    rc = fn(int(N), float(a), _dp(lam), _dp(W), _dp(table), len(ts), _dp(ts), _dp(out))
+    if rc:
+        raise ValueError(f"em_twin_{kind} rc={rc}")
+    return out

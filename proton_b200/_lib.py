@@ -47,7 +47,7 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_plan_scratch_bytes", "proton_em_eval", "proton_em_synchronize", "proton_em_stream",
            "proton_em_launch_count", "proton_em_analyze_host", "proton_em_run_cfg", "proton_em_debug_exp",
            "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read",
-           "proton_em_analyze_history_host"]
+           "proton_em_analyze_history_host", "proton_em_debug_line_table"]
 
 
 def load() -> ctypes.CDLL:
@@ -85,6 +85,8 @@ def load() -> ctypes.CDLL:
     lib.proton_em_profile.argtypes = [vp, ctypes.c_int]
     lib.proton_em_profile_read.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
                                            ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]
+    lib.proton_em_debug_line_table.argtypes = [vp, ctypes.c_int64, ctypes.c_int, vp, ctypes.c_int64,
+                                               ctypes.POINTER(ctypes.c_int64)]
     _lib = lib
     return lib
 

@@ -129,8 +129,9 @@ template <int R, int SIGN> struct DftBig {
         if (r == 0) t = o[r];
         else if (4 * r == R) t = mul_i<SIGN>(o[r]);
         else {
+          // (explicit FMAs, like every product-sum of these kernels: the CPU twin of the tests repeats them bit for bit)
           const double c = cos32(r * (32 / R)), s = (double)SIGN * sin32(r * (32 / R));
-          t = cplx{o[r].x * c - o[r].y * s, o[r].x * s + o[r].y * c};
+          t = cmul(o[r], cplx{c, s});
         }
         v[r] = cadd(e[r], t);
         v[r + R / 2] = csub(e[r], t);
@@ -351,7 +352,7 @@ __device__ __forceinline__ void fft_stage0_pruned(cplx* __restrict__ data, int g
         for (int q = 0; q < 8; ++q) {
           a[q] = (j + q * S < n_valid) ? d[pad_off<LOG2P, LOG2S>(q)] : cplx{0.0, 0.0};
           const double c = cos32(2 * q), sn = -sin32(2 * q);
-          b[q] = q == 0 ? a[q] : cplx{a[q].x * c - a[q].y * sn, a[q].x * sn + a[q].y * c};
+          b[q] = q == 0 ? a[q] : cmul(a[q], cplx{c, sn});
         }
         Dft<8, -1>::run(a);
         Dft<8, -1>::run(b);
@@ -400,8 +401,7 @@ __device__ __forceinline__ void fft_stage0_pruned(cplx* __restrict__ data, int g
 }
 
 // Middle of Bluestein: last DIF stage (s = 1), product with H, first DIT stage (s = 1) in registers.
-// HPAD: `hhat` is laid out like the data buffer (pad_idx), in shared or global memory; otherwise plain, in global memory.
-template <int LOG2P, int RADIX, int NT, bool HPAD = false>
+template <int LOG2P, int RADIX, int NT>
 __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, const cplx* __restrict__ hhat, int tid) {
   constexpr int P = 1 << LOG2P, NB = P / RADIX;
   constexpr int BSTEP = NB < NT ? NB : NT;
@@ -419,7 +419,7 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
         for (int q = 0; q < RADIX; ++q) v[q] = d[q];
         Dft<RADIX, -1>::run(v);
 #pragma unroll
-        for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], HPAD ? hhat[pbase + q] : ldg_cplx(hhat + base + q));
+        for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], ldg_cplx(hhat + base + q));
         Dft<RADIX, +1>::run(v);
 #pragma unroll
         for (int q = 0; q < RADIX; ++q) d[q] = v[q];
@@ -450,32 +450,26 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
 template <int LOG2P, int I> __host__ __device__ constexpr bool warp_local_after() {   // between stage I and stage I+1
   return I + 1 == plan_n(LOG2P) - 1 && plan_radix(LOG2P, I) == plan_radix(LOG2P, I + 1);
 }
-// A CTA can host several independent transforms, each run by a "team" of `nthr` threads that synchronise on their own
-// named barrier `barid` (1..15); barid == 0 is the whole CTA.
-__device__ __forceinline__ void team_sync(int barid, int nthr) {
-  if (barid == 0) __syncthreads();
-  else asm volatile("bar.sync %0, %1;" ::"r"(barid), "r"(nthr) : "memory");
-}
-template <int LOG2P, int I> __device__ __forceinline__ void stage_barrier(int barid = 0, int nthr = 0) {
-  if constexpr (warp_local_after<LOG2P, I>()) __syncwarp(); else team_sync(barid, nthr);
+template <int LOG2P, int I> __device__ __forceinline__ void stage_barrier() {
+  if constexpr (warp_local_after<LOG2P, I>()) __syncwarp(); else __syncthreads();
 }
 
 // Stage recursion helpers (compile-time unrolled over the plan).
 template <int LOG2P, int I, int IEND, int NT> struct DifStages {   // stages I .. IEND-1, SIGN = -1
-  static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid, int barid = 0) {
+  static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
     if constexpr (I < IEND) {
       fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), true, -1, NT, stage_tw_offset(LOG2P, I)>(data, gcount, tw, tid);
-      stage_barrier<LOG2P, I>(barid, NT);
-      DifStages<LOG2P, I + 1, IEND, NT>::run(data, gcount, tw, tid, barid);
+      stage_barrier<LOG2P, I>();
+      DifStages<LOG2P, I + 1, IEND, NT>::run(data, gcount, tw, tid);
     }
   }
 };
 template <int LOG2P, int I, int ISTOP, int NT> struct DitStages {   // stages I down to ISTOP, SIGN = +1
-  static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid, int barid = 0) {
+  static __device__ __forceinline__ void run(cplx* data, int gcount, const cplx* tw, int tid) {
     if constexpr (I >= ISTOP) {
       fft_stage<LOG2P, stage_radix<LOG2P, I>(), stage_log2s<LOG2P, I>(), false, +1, NT, stage_tw_offset(LOG2P, I)>(data, gcount, tw, tid);
-      if constexpr (I >= 1) stage_barrier<LOG2P, I - 1>(barid, NT); else team_sync(barid, NT);
-      DitStages<LOG2P, I - 1, ISTOP, NT>::run(data, gcount, tw, tid, barid);
+      if constexpr (I >= 1) stage_barrier<LOG2P, I - 1>(); else __syncthreads();
+      DitStages<LOG2P, I - 1, ISTOP, NT>::run(data, gcount, tw, tid);
     }
   }
 };

@@ -343,6 +343,12 @@ __global__ void em_exp_probe_kernel(const double* x, double* y, long long n, con
     y[i] = em_exp(x[i], exp_tab);
 }
 
+// cos(pi m / 2N), m < 4N: the cosine table em_eval_dense_kernel builds in shared memory (test hook for the CPU twin).
+__global__ void em_costab_probe_kernel(double* y, int N) {
+  for (int m = blockIdx.x * blockDim.x + threadIdx.x; m < 4 * N; m += gridDim.x * blockDim.x)
+    y[m] = em_cos_frac((unsigned long long)m, 2ULL * N);
+}
+
 // exp(x) - 1.0 as the fused kernels evaluate it (em_expm1_ref), for the parity test of the modal factor.
 __global__ void em_expm1_probe_kernel(const double* x, double* y, long long n) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)

@@ -25,7 +25,6 @@ constexpr int kLongLog2P2 = 12;
 constexpr int kLongP2 = 1 << kLongLog2P2;
 constexpr int kLongColsPerCta = 128;
 constexpr int kLongRowThreads = plan16(kLongLog2P2) ? 256 : 512;     // one butterfly of the outermost radix per thread
-constexpr int kLongRowPL = padded_len<kLongLog2P2>();                   // padded row length (complex elements)
 
 // Twiddles of the small column DFTs whose length is not a power of two: kDftTw[P1][m] = e^{+2 pi i m / P1}
 // (filled by the host at context creation).  Indices are compile-time constants after unrolling, so the values
@@ -408,16 +407,12 @@ __global__ void __launch_bounds__(kLongRowThreads, 2) em_long_row_kernel(const R
     if (p.mode == 1) {
       fft_stage<LOG2P, stage_radix<LOG2P, NST - 1>(), 0, true, -1, NT, 0>(data, 1, twb, tid);
       __syncthreads();
-      // H is stored row by row in the padded layout of the data buffer (kLongRowPL elements per row), so that the
-      // evaluation can take a row with one bulk copy; the pad slots are written as zeros
-      cplx* out = const_cast<cplx*>(p.tabs_build[s].hhat) + (long long)r * kLongRowPL;
-      for (int i = tid; i < kLongRowPL; i += NT) out[i] = cplx{0.0, 0.0};
-      __syncthreads();
-      for (int i = tid; i < P2; i += NT) out[pad_idx<LOG2P>(i)] = data[pad_idx<LOG2P>(i)];
+      cplx* out = const_cast<cplx*>(p.tabs_build[s].hhat) + (long long)r * P2;
+      for (int i = tid; i < P2; i += NT) out[i] = data[pad_idx<LOG2P>(i)];
       return;
     }
-    const cplx* hh = p.tabs[p.line_tab[p.tr_line[s]]].hhat + (long long)r * kLongRowPL;
-    fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT, true>(data, 1, hh, tid);
+    const cplx* hh = p.tabs[p.line_tab[p.tr_line[s]]].hhat + (long long)r * P2;
+    fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, 1, hh, tid);
     stage_barrier<LOG2P, NST - 2>();
     DitStages<LOG2P, NST - 2, 1, NT>::run(data, 1, twb, tid);
   } else {
@@ -437,88 +432,6 @@ __global__ void __launch_bounds__(kLongRowThreads, 2) em_long_row_kernel(const R
     DitStages<LOG2P, NST - 2, 1, NT>::run(data, 1, twb, tid);
   }
   row_dit_to_global<NT>(row, data, twb, tid);
-}
-
-// ---- row pass of the Bluestein evaluation, two rows per CTA sharing H through shared memory -------------------------
-// In em_long_row_kernel half of all stall samples sit in the middle phase, on the loads of this row's slice of the
-// transformed chirp H from L2 (ncu source page, profiles/r01).  All timestamp pairs of a line use the same H, and
-// consecutive transform slots belong to the same line, so one 512-thread CTA runs the row r of two consecutive slots
-// as two teams of 256 threads and fetches H[r] ONCE, by a bulk asynchronous copy (TMA, cp.async.bulk + mbarrier) that
-// is issued at kernel entry and lands — already in the padded layout, the table is stored that way — while the teams
-// run their first two stages.  The teams synchronise on their own named barriers, so they drift apart and one team's
-// shared-memory phases overlap the other's arithmetic.  Shared memory: twiddles + H + 2 rows = 209 KB, one CTA per SM.
-constexpr int kLongRow2Threads = 2 * kLongRowThreads;
-constexpr size_t kLongRow2Smem = (size_t)(stage_tw_total(kLongLog2P2) + 3 * kLongRowPL) * sizeof(cplx) + 16;
-
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// global -> this CTA's shared memory, completion counted in bytes on `bar` (16-byte aligned addresses and size)
-__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
-  asm volatile(
-      "{\n.reg .pred p;\nWAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(bar), "r"(parity) : "memory");
-}
-
-__global__ void __launch_bounds__(kLongRow2Threads, 1) em_long_row2_kernel(const RowParams p, const int n_tr) {
-  constexpr int LOG2P = kLongLog2P2, P2 = kLongP2, NT = kLongRowThreads, NST = plan_n(LOG2P), PL = kLongRowPL;
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  cplx* twb = reinterpret_cast<cplx*>(smem_raw);
-  cplx* hh = twb + stage_tw_total(LOG2P);
-  cplx* data0 = hh + PL;
-  unsigned long long* bar_p = reinterpret_cast<unsigned long long*>(data0 + 2 * PL);
-  const int tid = threadIdx.x, team = tid >> 8, tt = tid & (NT - 1);
-  const int r = blockIdx.x;
-  const int s_first = blockIdx.y * 2, s = s_first + team;
-  const bool active = s < n_tr;
-  pdl_launch_dependents();
-  // H does not come from the preceding kernel: its copy starts before the dependency wait
-  const int line0 = p.tr_line[s_first];
-  const cplx* hh_g = p.tabs[p.line_tab[line0]].hhat + (long long)r * PL;
-  const unsigned bar = smem_u32(bar_p);
-  if (tid == 0) {
-    mbar_init(bar, 1);
-    mbar_expect_tx(bar, PL * (unsigned)sizeof(cplx));
-    bulk_g2s(smem_u32(hh), hh_g, PL * (unsigned)sizeof(cplx), bar);
-  }
-  for (int i = tid; i < stage_tw_total(LOG2P); i += kLongRow2Threads) twb[i] = p.tw[i];
-  bool shared_h = true;
-  if (active && team == 1) {
-    const int line1 = p.tr_line[s];
-    if (line1 != line0) {            // the second slot belongs to the next line: its H comes straight from global memory
-      shared_h = false;
-      hh_g = p.tabs[p.line_tab[line1]].hhat + (long long)r * PL;
-    }
-  }
-  pdl_wait();                        // the rows come from the preceding column kernel
-  __syncthreads();                   // twiddles in place, barrier initialised
-  if (!active) return;
-  cplx* data = data0 + team * PL;
-  const int barid = 1 + team;
-  const long long P = (long long)P2 * p.p1;
-  cplx* row = p.x + (long long)s * P + (long long)r * P2;
-  row_dif_from_global<NT>(row, data, twb, tt);
-  team_sync(barid, NT);
-  DifStages<LOG2P, 1, NST - 1, NT>::run(data, 1, twb, tt, barid);
-  if (shared_h) {
-    mbar_wait(bar, 0);
-    fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT, true>(data, 1, hh, tt);
-  } else {
-    fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT, true>(data, 1, hh_g, tt);
-  }
-  stage_barrier<LOG2P, NST - 2>(barid, NT);
-  DitStages<LOG2P, NST - 2, 1, NT>::run(data, 1, twb, tt, barid);
-  row_dit_to_global<NT>(row, data, twb, tt);
 }
 
 // ---- inverse column pass + epilogue -----------------------------------------------------------------------

@@ -380,7 +380,6 @@ inline size_t long_pair_smem(int p1) { return ((size_t)(p1 + 1) / 2 + 1) * 128 *
 
 int init_long_attrs() {
   CU_TRY(cudaFuncSetAttribute(em::em_long_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLongRowSmem));
-  CU_TRY(cudaFuncSetAttribute(em::em_long_row2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)em::kLongRow2Smem));
 #define M(q)                                                                                                              \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_col_smem(q)));        \
   CU_TRY(cudaFuncSetAttribute(em::em_long_colfwd_paired_kernel<q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)long_pair_smem(q)));
@@ -505,28 +504,9 @@ int launch_long_scatter(proton_em_ctx* ctx, cudaStream_t st, int p1, const em::L
   return PROTON_EM_OK;
 }
 
-// Row pass.  The Bluestein evaluation (mode 0) runs two rows per CTA with H staged in shared memory by a bulk copy
-// (em_long_row2_kernel; PROTON_EM_ROW2=0 selects the one-row kernel); table build and power-of-two lines use the one-row kernel.
-bool row2_enabled() {
-  static const bool v = [] { const char* e = std::getenv("PROTON_EM_ROW2"); return !(e && std::atoi(e) == 0); }();
-  return v;
-}
 int launch_long_row(proton_em_ctx* ctx, cudaStream_t st, const em::RowParams& rp, int n_tr) {
-  ProfScope prof(ctx, PK_LONG_ROW, st);
-  if (rp.mode == 0 && row2_enabled()) {
-    const dim3 grid2(rp.p1, (n_tr + 1) / 2);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid2; cfg.blockDim = dim3(em::kLongRow2Threads); cfg.dynamicSmemBytes = em::kLongRow2Smem; cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 1 : 0;
-    CU_TRY(cudaLaunchKernelEx(&cfg, em::em_long_row2_kernel, rp, n_tr));
-    ctx->launches++;
-    CU_TRY(cudaGetLastError());
-    return PROTON_EM_OK;
-  }
   const dim3 grid(rp.p1, n_tr);
+  ProfScope prof(ctx, PK_LONG_ROW, st);
   CU_TRY(launch_pdl(em::em_long_row_kernel, grid, em::kLongRowThreads, kLongRowSmem, st, rp));
   ctx->launches++;
   CU_TRY(cudaGetLastError());
@@ -618,7 +598,7 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
       t.post = static_cast<const em::cplx*>(p);
-      const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongRowPL : ((size_t)1 << c.log2p);
+      const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2 : ((size_t)1 << c.log2p);
       CU_TRY(ctx->arena.alloc(&p, plen * sizeof(em::cplx)));
       t.hhat = static_cast<const em::cplx*>(p);
     }
@@ -1464,6 +1444,44 @@ int proton_em_analyze_history_host(proton_em_ctx* ctx, const proton_em_batch* b,
 }
 
 static int debug_exp_impl(proton_em_ctx* ctx, const double* x, double* y, int64_t n, int which);
+
+int proton_em_debug_line_table(proton_em_plan* p, int64_t line, int which, double* out, int64_t capacity, int64_t* count) {
+  if (!p || !out || !count) return fail(PROTON_EM_EINVAL, "proton_em_debug_line_table: NULL argument");
+  if (line < 0 || line >= p->L) return fail(PROTON_EM_EINVAL, "line %lld out of range", (long long)line);
+  proton_em_ctx* ctx = p->ctx;
+  { int rc = set_device(ctx); if (rc) return rc; }
+  const int N = p->num_nodes[line];
+  const auto it = ctx->tabs.find(N);
+  if (it == ctx->tabs.end()) return fail(PROTON_EM_EINVAL, "no tables for N = %d", N);
+  const em::NTab& t = it->second;
+  const void* src = nullptr;
+  int64_t n = 0;
+  switch (which) {
+    case 0: src = t.lam; n = N; break;
+    case 1: src = p->d_W.p + p->node_off[line]; n = N; break;
+    case 2: src = t.pre; n = t.pre ? 2LL * N : 0; break;
+    case 3: src = t.post; n = t.post ? 2LL * N : 0; break;
+    case 4: n = 4LL * N; break;
+    default: return fail(PROTON_EM_EINVAL, "unknown table %d", which);
+  }
+  *count = n;
+  if (n > capacity) return fail(PROTON_EM_EINVAL, "table has %lld doubles, the buffer %lld", (long long)n, (long long)capacity);
+  if (n == 0) return PROTON_EM_OK;
+  CU_TRY(cudaStreamSynchronize(ctx->stream));
+  if (which == 4) {
+    DevBuf<double> tmp;
+    struct G { DevBuf<double>& b; ~G() { b.free(); } } g{tmp};
+    CU_TRY(tmp.alloc((size_t)n));
+    em::em_costab_probe_kernel<<<8, 256, 0, ctx->stream>>>(tmp.p, N);
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
+    CU_TRY(cudaMemcpyAsync(out, tmp.p, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU_TRY(cudaStreamSynchronize(ctx->stream));
+    return PROTON_EM_OK;
+  }
+  CU_TRY(cudaMemcpy(out, src, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
+  return PROTON_EM_OK;
+}
 
 int proton_em_debug_exp(proton_em_ctx* ctx, const double* x, double* y, int64_t n) { return debug_exp_impl(ctx, x, y, n, 0); }
 int proton_em_debug_expm1(proton_em_ctx* ctx, const double* x, double* y, int64_t n) { return debug_exp_impl(ctx, x, y, n, 1); }
