@@ -92,6 +92,14 @@ const char* proton_em_version(void);
  * its dense N x N matrices stop it near N = 30 000 on a 16 GB host).  The same limit holds for proton_em_run_cfg and
  * proton_em_analyze_host. */
 int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* batch, int location, proton_em_plan** out);
+/* The same with an initial stress (restart from a stress field; no counterpart in the reference, whose
+ * kernel starts from zero stress — bin/EMtool_analytical@0xc68c has no sigma_0 input).  `sigma0` holds one value per
+ * node, line l at node_off[l] (the layout of one timestamp's rows of proton_em_result.stress, so the field evaluated at
+ * one time can be handed back in as the state to continue from, possibly with other currents).  The plan keeps its own
+ * copy.  The dense forward DCT-II of the field costs O(N^2) per line, once per pack.  Evaluation of such a plan returns
+ *     sigma(t) = V exp(Lambda a t) V^T sigma0  +  the reference's closed form for the batch's currents. */
+int proton_em_pack_sigma0(proton_em_ctx* ctx, const proton_em_batch* batch, const double* sigma0, int location,
+                          proton_em_plan** out);
 int proton_em_plan_destroy(proton_em_plan* plan);
 int64_t proton_em_plan_total_nodes(const proton_em_plan* plan);
 int64_t proton_em_plan_num_lines(const proton_em_plan* plan);

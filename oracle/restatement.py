@@ -166,6 +166,34 @@ def history_batch(num_nodes, a_coeff, trip_off, rows, cols, vals, u_off, curden_
     return total, mx, amx
 
 
+def sigma0_batch(num_nodes, a_coeff, trip_off, rows, cols, vals, u_off, curden, sigma0, ts, use_double=False):
+    """Evolution from an initial stress field (product: proton_em_pack_sigma0; no counterpart in the reference, whose
+    kernel starts from zero stress):  sigma(t) = V exp(Lambda a t) V^T sigma0 + the reference closed form for the
+    currents, V = the DCT-II basis, lambda_k as the reference computes it.  The homogeneous part is restated with
+    scipy.fft (DCT-II forward, DCT-III back) — another transform code than either the GPU path or em_oracle.c — and
+    pinned in tests/test_sigma0.py against a stiff ODE integration of d sigma/dt = a L sigma + B u from sigma0.
+    -> (stress, max[L,T], argmax[L,T])"""
+    from scipy.fft import dct
+    ts = np.ascontiguousarray(np.atleast_1d(ts), dtype=np.float64)
+    num_nodes = np.ascontiguousarray(num_nodes, dtype=np.int32)
+    a_coeff = np.ascontiguousarray(a_coeff, dtype=np.float64)
+    sigma0 = np.ascontiguousarray(sigma0, dtype=np.float64).reshape(-1)
+    total, _, _ = batch(num_nodes, a_coeff, trip_off, rows, cols, vals, u_off, curden, ts, use_double=use_double)
+    total = total.copy()
+    L, T = len(num_nodes), len(ts)
+    off = np.concatenate([[0], np.cumsum(num_nodes.astype(np.int64))])
+    mx = np.empty((L, T)); amx = np.empty((L, T), np.int32)
+    for l in range(L):
+        N = int(num_nodes[l])
+        lam = reference_lambda(N)
+        y = dct(sigma0[off[l]:off[l + 1]], type=2) / (2.0 * N)            # y_k = (1/N) sum_n x_n cos(..)
+        blk = total[off[l] * T:off[l + 1] * T].reshape(T, N)
+        for j, t in enumerate(ts):
+            blk[j] += dct(y * np.exp(lam * (a_coeff[l] * t)), type=3)    # x_0 + 2 sum_{k>=1} x_k cos(..)
+        mx[l] = blk.max(axis=1); amx[l] = blk.argmax(axis=1)
+    return total, mx, amx
+
+
 def max_threads() -> int:
     return int(load().em_oracle_max_threads())
 

@@ -47,7 +47,7 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_plan_scratch_bytes", "proton_em_eval", "proton_em_synchronize", "proton_em_stream",
            "proton_em_launch_count", "proton_em_analyze_host", "proton_em_run_cfg", "proton_em_debug_exp",
            "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read",
-           "proton_em_analyze_history_host", "proton_em_debug_line_table"]
+           "proton_em_analyze_history_host", "proton_em_debug_line_table", "proton_em_pack_sigma0"]
 
 
 def load() -> ctypes.CDLL:
@@ -64,6 +64,7 @@ def load() -> ctypes.CDLL:
     lib.proton_em_last_error.restype = ctypes.c_char_p
     lib.proton_em_version.restype = ctypes.c_char_p
     lib.proton_em_pack.argtypes = [vp, ctypes.POINTER(Batch), ctypes.c_int, ctypes.POINTER(vp)]
+    lib.proton_em_pack_sigma0.argtypes = [vp, ctypes.POINTER(Batch), vp, ctypes.c_int, ctypes.POINTER(vp)]
     lib.proton_em_plan_destroy.argtypes = [vp]
     for f in (lib.proton_em_plan_total_nodes, lib.proton_em_plan_num_lines, lib.proton_em_plan_scratch_bytes,
               lib.proton_em_launch_count):

@@ -168,10 +168,17 @@ class Context:
     def synchronize(self):
         check(self._lib.proton_em_synchronize(self._h))
 
-    def pack(self, batch: LineBatch) -> "Plan":
+    def pack(self, batch: LineBatch, sigma0=None) -> "Plan":
+        """`sigma0`: optional initial stress, one value per node (line l at node_off[l]); see proton_em_pack_sigma0."""
         h = ctypes.c_void_p()
         cb = batch._as_c()
-        check(self._lib.proton_em_pack(self._h, ctypes.byref(cb), HOST, ctypes.byref(h)))
+        if sigma0 is None:
+            check(self._lib.proton_em_pack(self._h, ctypes.byref(cb), HOST, ctypes.byref(h)))
+        else:
+            s0 = np.ascontiguousarray(sigma0, dtype=np.float64).reshape(-1)
+            if s0.size != batch.total_nodes:
+                raise ValueError("sigma0 needs one value per node of the batch")
+            check(self._lib.proton_em_pack_sigma0(self._h, ctypes.byref(cb), s0.ctypes.data, HOST, ctypes.byref(h)))
         return Plan(self, h, batch.node_off, keep=None)
 
     def pack_device(self, num_nodes, a_coeff, trip_off, trip_row, trip_col, trip_val, u_off, curden) -> "Plan":

@@ -506,4 +506,169 @@ __global__ void __launch_bounds__(128) em_rowmax_kernel(const RowMaxParams p) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Initial stress (no counterpart in the reference, whose kernel starts from zero stress,
+// bin/EMtool_analytical@0xc68c).  With sigma(0) = sigma0 the discretised equation has the solution
+//     sigma(t) = sigma0 + sum_k [ (W_k + Z_k) (e^{lambda_k a t} - 1) ] cos(..)  + t W_0,   Z_k = DCT-II(sigma0)_k / N,
+// i.e. the kernels above evaluate it unchanged once Z is folded into the modal weights (k >= 1), and sigma0 itself is
+// added to every timestamp's row afterwards.  Two kernels:
+//   em_forward_sigma0_kernel  dense forward DCT-II of a field: W_k += (1/N) sum_n sigma0[n] cos(pi k (2n+1) / 2N), k >= 1.
+//       One CTA per (line, slab of 4096 modes), one thread per 32 consecutive modes; the field streams through shared
+//       memory in chunks fetched by bulk asynchronous copies (TMA, cp.async.bulk + mbarrier, two buffers: the next chunk
+//       lands while this one is consumed).  Cosines: exact integer angle at every 64th node, in between two rotations
+//       (along n and along k), so the cost is ~5 FP64 instructions per (mode, node) pair.  O(N^2) per line: a grid's
+//       worth (sum N^2 ~ 1e11) takes tens of milliseconds, once per restart.
+//   em_add_sigma0_kernel      stress[t][n] += sigma0[n] for the rows of a launch, with max / argmax / flag of the sums.
+// ---------------------------------------------------------------------------------------------
+constexpr int kS0Chunk = 2048;            // doubles per staged chunk (16 KB)
+constexpr int kS0Modes = 32;              // modes per thread
+constexpr int kS0Threads = 128;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// global -> this CTA's shared memory, completion counted in bytes on `bar` (16-byte aligned addresses and size).
+// The source is always memory of this GPU (a plan-owned copy of the field).
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(bar), "r"(parity) : "memory");
+}
+
+struct Sigma0Params {
+  const int* num_nodes;
+  const long long* node_off;
+  const long long* slab_off;     // [L+1] prefix sum of ceil(N / 4096): CTA -> (line, slab)
+  long long num_lines;
+  const double* sigma0;          // plan-owned copy, line l at node_off[l]; two doubles of slack at the end
+  double* W;
+};
+
+__global__ void __launch_bounds__(kS0Threads) em_forward_sigma0_kernel(const Sigma0Params p) {
+  __shared__ __align__(16) double buf[2][kS0Chunk + 2];
+  __shared__ __align__(8) unsigned long long bars[2];
+  const long long line = find_line(p.slab_off, p.num_lines, (long long)blockIdx.x);
+  const int slab = (int)((long long)blockIdx.x - p.slab_off[line]);
+  const int N = p.num_nodes[line];
+  const long long noff = p.node_off[line];
+  const int tid = threadIdx.x;
+  const int k0 = (slab * kS0Threads + tid) * kS0Modes;
+  // chunks start on even global elements so that every bulk copy is 16-byte aligned: element `shift` of the first
+  // buffer is node 0 of the line
+  const int shift = (int)(noff & 1);
+  const double* src0 = p.sigma0 + (noff - shift);
+  const int total = N + shift;                                   // doubles from src0 to the end of the line
+  const int nchunks = (total + kS0Chunk - 1) / kS0Chunk;
+  const unsigned bar0 = smem_u32(&bars[0]), bar1 = smem_u32(&bars[1]);
+  auto issue = [&](int c) {
+    const int len = min(kS0Chunk, total - c * kS0Chunk);
+    const unsigned bytes = (unsigned)(((len + 1) & ~1) * sizeof(double));      // (the slack behind the array covers the pad)
+    const unsigned bar = (c & 1) ? bar1 : bar0;
+    mbar_expect_tx(bar, bytes);
+    bulk_g2s(smem_u32(&buf[c & 1][0]), src0 + (long long)c * kS0Chunk, bytes, bar);
+  };
+  if (tid == 0) {
+    mbar_init(bar0, 1);
+    mbar_init(bar1, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0) { issue(0); if (nchunks > 1) issue(1); }
+  double R[kS0Modes];
+#pragma unroll
+  for (int q = 0; q < kS0Modes; ++q) R[q] = 0.0;
+  const bool live = k0 < N;
+  const unsigned long long den = 2ULL * (unsigned long long)N;
+  // per-thread constants: step of the k0-angle and of the base angle when n advances by one
+  const cplx dz = em_cis_frac((2ULL * (unsigned long long)k0) % (2ULL * den), den);     // e^{i pi 2 k0 / 2N}
+  const cplx dw = em_cis_frac(2ULL, den);                                               // e^{i pi 2 / 2N}
+  cplx z = cplx{1.0, 0.0}, w = cplx{1.0, 0.0};
+  for (int c = 0; c < nchunks; ++c) {
+    mbar_wait((c & 1) ? bar1 : bar0, (unsigned)((c >> 1) & 1));
+    const double* b = buf[c & 1];
+    const int e0 = c * kS0Chunk;                                  // first element (relative to src0) of this chunk
+    const int len = min(kS0Chunk, total - e0);
+    if (live) {
+      for (int e = (c == 0 ? shift : 0); e < len; ++e) {
+        const int n = e0 + e - shift;                             // node index
+        if ((n & 63) == 0) {                                      // exact angles every 64 nodes
+          const unsigned long long m = 2ULL * (unsigned long long)n + 1ULL;
+          w = em_cis_frac(m, den);
+          z = em_cis_frac((m * (unsigned long long)k0) % (2ULL * den), den);
+        }
+        const double x = b[e];
+        cplx zz = z;
+#pragma unroll
+        for (int q = 0; q < kS0Modes; ++q) {
+          R[q] = fma(x, zz.x, R[q]);
+          zz = cmul(zz, w);
+        }
+        z = cmul(z, dz);
+        w = cmul(w, dw);
+      }
+    }
+    __syncthreads();                                              // everyone is done with this buffer
+    if (tid == 0 && c + 2 < nchunks) issue(c + 2);
+  }
+  if (live) {
+    double* W = p.W + noff + k0;
+#pragma unroll
+    for (int q = 0; q < kS0Modes; ++q)
+      if (k0 + q < N && k0 + q >= 1) W[q] = W[q] + R[q] / (double)N;
+  }
+}
+
+struct AddSigma0Params {
+  double* stress;              // indexed by global node offset (node_off[line] * T + t * N)
+  const double* sigma0;
+  const long long* node_off;
+  const int* num_nodes;
+  long long line0;             // first line of this launch
+  int T;
+  double* mx; int* amx; unsigned char* flag;
+  double critical;
+};
+
+__global__ void __launch_bounds__(128) em_add_sigma0_kernel(const AddSigma0Params p) {
+  const long long row = blockIdx.x;
+  const long long line = p.line0 + row / p.T;
+  const int tj = (int)(row % p.T);
+  const int N = p.num_nodes[line];
+  double* dst = p.stress + p.node_off[line] * (long long)p.T + (long long)tj * N;
+  const double* s0 = p.sigma0 + p.node_off[line];
+  double best = -__longlong_as_double(0x7ff0000000000000LL);
+  int besti = 0x7fffffff;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    const double v = dst[n] + s0[n];
+    dst[n] = v;
+    if (v > best) { best = v; besti = n; }
+  }
+  __shared__ double sv[4];
+  __shared__ int si[4];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const double ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+    if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = besti; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int q = 1; q < 4; ++q)
+      if (sv[q] > best || (sv[q] == best && si[q] < besti)) { best = sv[q]; besti = si[q]; }
+    if (besti == 0x7fffffff) { besti = 0; best = dst[0]; }
+    const long long o = line * p.T + tj;
+    p.mx[o] = best; p.amx[o] = besti; p.flag[o] = (best > p.critical) ? 1 : 0;
+  }
+}
+
 }  // namespace em

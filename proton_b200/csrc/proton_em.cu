@@ -281,6 +281,7 @@ struct proton_em_plan {
   DevBuf<double> d_r_val, d_W;
   DevBuf<em::NTab> d_tabs;
   DevBuf<int> d_class_lines;     // concatenated per-class line lists
+  DevBuf<double> d_sigma0;       // initial stress per node (+2 doubles of slack), empty when the plan starts from zero stress
   struct ClassList { LineClass cls; int log2p; int offset; int count; };
   // Lines are evaluated in chunks of contiguous lines (one chunk unless the host path asked for more, so
   // that the device-to-host copy of one chunk overlaps the evaluation of the next).
@@ -650,7 +651,7 @@ void destroy_plan(proton_em_plan* p) {
   if (!p) return;
   p->own_num_nodes.free(); p->own_a.free(); p->own_trip_off.free();
   p->d_node_off.free(); p->d_blk_off.free(); p->d_r_idx.free(); p->d_r_cnt.free(); p->d_line_tab.free();
-  p->d_r_val.free(); p->d_W.free(); p->d_tabs.free(); p->d_class_lines.free();
+  p->d_r_val.free(); p->d_W.free(); p->d_tabs.free(); p->d_class_lines.free(); p->d_sigma0.free();
   for (auto* ll : p->long_lists) { ll->line.free(); ll->pair.free(); delete ll; }
   delete p;
 }
@@ -838,13 +839,21 @@ int64_t proton_em_plan_scratch_bytes(const proton_em_plan* p) {
                    p->d_r_val.bytes() + p->d_W.bytes() + p->d_tabs.bytes() + p->d_class_lines.bytes());
 }
 
-static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out);
+static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out,
+                     const double* sigma0 = nullptr);
 
 int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, proton_em_plan** out) {
   return pack_impl(ctx, b, location, 0, out);
 }
 
-static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out) {
+int proton_em_pack_sigma0(proton_em_ctx* ctx, const proton_em_batch* b, const double* sigma0, int location,
+                          proton_em_plan** out) {
+  if (!sigma0 && b && b->num_lines > 0) return fail(PROTON_EM_EINVAL, "proton_em_pack_sigma0: sigma0 is NULL");
+  return pack_impl(ctx, b, location, 0, out, sigma0);
+}
+
+static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out,
+                     const double* sigma0) {
   if (!ctx || !b || !out) return fail(PROTON_EM_EINVAL, "proton_em_pack: NULL argument");
   *out = nullptr;
   if (location != PROTON_EM_HOST && location != PROTON_EM_DEVICE) return fail(PROTON_EM_EINVAL, "bad location %d", location);
@@ -1024,6 +1033,27 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
   em::em_forward_kernel<<<fwd_grid, 128, 0, st>>>(fp);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
+  DevBuf<long long> d_slab_off;
+  struct SlabGuard { DevBuf<long long>& b; ~SlabGuard() { b.free(); } } sguard{d_slab_off};
+  std::vector<long long> slab_off;
+  if (sigma0) {
+    // initial stress: a plan-owned copy of the field, its dense forward DCT-II folded into the modal weights
+    CU_TRY(p->d_sigma0.alloc((size_t)p->total_nodes + 2));
+    CU_TRY(cudaMemsetAsync(p->d_sigma0.p + p->total_nodes, 0, 2 * sizeof(double), st));
+    CU_TRY(cudaMemcpyAsync(p->d_sigma0.p, sigma0, (size_t)p->total_nodes * sizeof(double),
+                           location == PROTON_EM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+    const int slab = em::kS0Threads * em::kS0Modes;
+    slab_off.resize(L + 1);
+    slab_off[0] = 0;
+    for (int64_t i = 0; i < L; ++i) slab_off[i + 1] = slab_off[i] + (p->num_nodes[i] + slab - 1) / slab;
+    if (slab_off[L] > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many lines for the initial-stress transform");
+    CU_TRY(d_slab_off.alloc(L + 1));
+    CU_TRY(cudaMemcpyAsync(d_slab_off.p, slab_off.data(), (L + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+    em::Sigma0Params sp{p->d_num_nodes, p->d_node_off.p, d_slab_off.p, L, p->d_sigma0.p, p->d_W.p};
+    em::em_forward_sigma0_kernel<<<(unsigned)slab_off[L], em::kS0Threads, 0, st>>>(sp);
+    ctx->launches++;
+    CU_TRY(cudaGetLastError());
+  }
   int err = 0;
   CU_TRY(cudaMemcpyAsync(&err, d_err.p, sizeof(int), cudaMemcpyDeviceToHost, st));
   CU_TRY(cudaStreamSynchronize(st));
@@ -1150,9 +1180,42 @@ static int eval_long_finish(proton_em_plan* p, const proton_em_plan::LongList* l
   return PROTON_EM_OK;
 }
 
+static int eval_device_core(proton_em_plan* p, const double* d_ts, int T, const proton_em_opts* opts,
+                            double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag,
+                            int chunk_begin, int chunk_end);
+
+// Evaluation of the chunks [chunk_begin, chunk_end).  A plan packed with an initial stress (proton_em_pack_sigma0) has
+// its forward DCT folded into the modal weights already; what is left is to add sigma0 to every timestamp's row and to
+// take the reductions of the sums (em_add_sigma0_kernel; needs a field, so a reduce-only call gets a temporary one).
 static int eval_device(proton_em_plan* p, const double* d_ts, int T, const proton_em_opts* opts,
                        double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag,
                        int chunk_begin = 0, int chunk_end = -1) {
+  if (p->d_sigma0.n == 0) return eval_device_core(p, d_ts, T, opts, d_stress, d_mx, d_amx, d_flag, chunk_begin, chunk_end);
+  proton_em_ctx* ctx = p->ctx;
+  const int c_end = chunk_end < 0 ? (int)p->chunks.size() : chunk_end;
+  if (chunk_begin >= c_end) return PROTON_EM_OK;
+  const long long l0 = p->chunks[chunk_begin].l0, l1 = p->chunks[c_end - 1].l1;
+  const long long n0 = p->node_off[l0], n1 = p->node_off[l1];
+  const long long rows = (l1 - l0) * T;
+  if (rows > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many (line, timestamp) rows in one evaluation");
+  DevBuf<double> tmp;
+  struct G { DevBuf<double>& b; ~G() { b.free(); } } g{tmp};
+  if (!d_stress) {
+    CU_TRY(tmp.alloc((size_t)(n1 - n0) * T));
+    d_stress = tmp.p - n0 * (long long)T;                       // kernels index by global node offset
+  }
+  { int rc = eval_device_core(p, d_ts, T, opts, d_stress, d_mx, d_amx, d_flag, chunk_begin, chunk_end); if (rc) return rc; }
+  em::AddSigma0Params ap{d_stress, p->d_sigma0.p, p->d_node_off.p, p->d_num_nodes, l0, T, d_mx, d_amx, d_flag,
+                         opts ? opts->critical_stress : NAN};
+  em::em_add_sigma0_kernel<<<(unsigned)rows, 128, 0, ctx->stream>>>(ap);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+static int eval_device_core(proton_em_plan* p, const double* d_ts, int T, const proton_em_opts* opts,
+                            double* d_stress, double* d_mx, int* d_amx, unsigned char* d_flag,
+                            int chunk_begin, int chunk_end) {
   proton_em_ctx* ctx = p->ctx;
   const double critical = opts ? opts->critical_stress : NAN;
   const int alg = opts ? opts->algorithm : PROTON_EM_ALG_AUTO;
