@@ -524,25 +524,6 @@ constexpr int kS0Chunk = 2048;            // doubles per staged chunk (16 KB)
 constexpr int kS0Modes = 32;              // modes per thread
 constexpr int kS0Threads = 128;
 
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// global -> this CTA's shared memory, completion counted in bytes on `bar` (16-byte aligned addresses and size).
-// The source is always memory of this GPU (a plan-owned copy of the field).
-__device__ __forceinline__ void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
-  asm volatile(
-      "{\n.reg .pred p;\nWAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(bar), "r"(parity) : "memory");
-}
 
 struct Sigma0Params {
   const int* num_nodes;
@@ -579,7 +560,7 @@ __global__ void __launch_bounds__(kS0Threads) em_forward_sigma0_kernel(const Sig
   if (tid == 0) {
     mbar_init(bar0, 1);
     mbar_init(bar1, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_init_fence();
   }
   __syncthreads();
   if (tid == 0) { issue(0); if (nchunks > 1) issue(1); }

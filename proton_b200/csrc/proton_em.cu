@@ -155,6 +155,18 @@ struct Arena {
     left -= bytes;
     return cudaSuccess;
   }
+  // One block for everything a batch of new tables needs, instead of a cudaMalloc per 32 MB.
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= left) return cudaSuccess;
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return e;
+    blocks.push_back(p);
+    cur = static_cast<char*>(p);
+    left = bytes;
+    total += bytes;
+    return cudaSuccess;
+  }
   void release() {
     for (void* p : blocks) cudaFree(p);
     blocks.clear();
@@ -543,9 +555,9 @@ int long_build_tables(proton_em_ctx* ctx, const em::NTab* d_e, int count, int lp
 // exp(lambda a t) - 1 cancels.
 void host_lambda(int N, double* out) {
   const double pi = 3.141592653589793115997963468544185161590576171875;
-  for (int k = 0; k < N; ++k) {
-    volatile double c = std::cos((double)k * pi / (double)N);
-    volatile double c2 = c + c;
+  for (int k = 0; k < N; ++k) {                   // (host code is built with -ffp-contract=off: three roundings, as written)
+    const double c = std::cos((double)k * pi / (double)N);
+    const double c2 = c + c;
     out[k] = c2 - 2.0;
   }
 }
@@ -556,28 +568,26 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
   for (int N : distinct)
     if (ctx->tabs.find(N) == ctx->tabs.end()) fresh.push_back(N);
   if (fresh.empty()) return PROTON_EM_OK;
+  Trace tr("ensure_tables");
   size_t total = 0;
   std::vector<size_t> off(fresh.size());
   for (size_t i = 0; i < fresh.size(); ++i) { off[i] = total; total += (size_t)fresh[i]; }
-  std::vector<double> lam(total);
   {
-    unsigned nth = std::thread::hardware_concurrency();
-    if (nth == 0) nth = 1;
-    if (total < (size_t)1 << 16) nth = 1;
-    nth = std::min<unsigned>(nth, 64);
-    std::vector<std::thread> pool;
-    std::vector<size_t> order(fresh.size());
-    for (size_t i = 0; i < order.size(); ++i) order[i] = i;
-    auto work = [&](unsigned w) {
-      for (size_t i = w; i < fresh.size(); i += nth) host_lambda(fresh[i], lam.data() + off[i]);
-    };
-    for (unsigned w = 1; w < nth; ++w) pool.emplace_back(work, w);
-    work(0);
-    for (auto& t : pool) t.join();
+    // everything the new lengths need, in one allocation
+    size_t need = ((total * sizeof(double) + 255) & ~size_t(255)) + ((fresh.size() * sizeof(em::NTab) + 255) & ~size_t(255));
+    for (int N : fresh) {
+      const ClassOf c = classify(N);
+      const size_t nb = ((size_t)N * sizeof(em::cplx) + 255) & ~size_t(255);
+      if (c.cls != CLS_SMALL) need += nb;
+      if (c.cls == CLS_BLUE || c.cls == CLS_LBLUE) {
+        const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2 : ((size_t)1 << c.log2p);
+        need += nb + ((plen * sizeof(em::cplx) + 255) & ~size_t(255));
+      }
+    }
+    CU_TRY(ctx->arena.reserve(need));
   }
   void* d_lam = nullptr;
   CU_TRY(ctx->arena.alloc(&d_lam, total * sizeof(double)));
-  CU_TRY(cudaMemcpyAsync(d_lam, lam.data(), total * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   // group the new entries by (class, log2p) for the table kernels
   std::vector<em::NTab> entries(fresh.size());
   for (size_t i = 0; i < fresh.size(); ++i) {
@@ -605,6 +615,7 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
     }
     entries[i] = t;
   }
+  tr.lap("arena + entries");
   // One upload of all new entries (grouped by kernel), then one table launch per group, all on the context stream
   // and without host synchronisation in between.
   std::vector<em::NTab> sorted;
@@ -638,7 +649,28 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
       if (rc) { cudaStreamSynchronize(ctx->stream); return rc; }
     }
   }
+  tr.lap("table kernels queued");
+  // lambda_k on the host cores while the GPU builds the chirp tables (which do not depend on it)
+  std::vector<double> lam(total);
+  {
+    unsigned nth = std::thread::hardware_concurrency();
+    if (nth == 0) nth = 1;
+    if (total < (size_t)1 << 16) nth = 1;
+    nth = std::min<unsigned>(nth, 64);
+    std::vector<std::thread> pool;
+    std::vector<size_t> order(fresh.size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = i;
+    auto work = [&](unsigned w) {
+      for (size_t i = w; i < fresh.size(); i += nth) host_lambda(fresh[i], lam.data() + off[i]);
+    };
+    for (unsigned w = 1; w < nth; ++w) pool.emplace_back(work, w);
+    work(0);
+    for (auto& t : pool) t.join();
+  }
+  tr.lap("host lambda");
+  CU_TRY(cudaMemcpyAsync(d_lam, lam.data(), total * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   CU_TRY(cudaStreamSynchronize(ctx->stream));   // lam upload must finish before `lam` goes away
+  tr.lap("sync");
   for (const em::NTab& t : entries) ctx->tabs[t.n] = t;
   return PROTON_EM_OK;
 }
