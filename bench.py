@@ -177,19 +177,25 @@ def fp64_peak():
         return 1.8e13, 36.0, "fallback (B200: 64 FP64 lanes x 148 SMs x 1.9 GHz)"
 
 
-def fp64_counters(workload):
-    """Executed FP64 thread-instructions per step and per kernel family, from the committed ncu launch list of this
-    command (tools/launch_summary.py --json).  None when no counter file exists for the workload."""
-    for name in (f"r02_fp64_counters_{workload}.json",):
-        p = REPO / "profiles" / name
-        if p.exists():
-            d = json.loads(p.read_text())
-            fam = {}
-            for k, v in d.get("kernels", {}).items():
-                fam.setdefault(kernel_family(k), 0.0)
-                fam[kernel_family(k)] += v.get("dadd", 0.0) + v.get("dmul", 0.0) + v.get("dfma", 0.0)
-            return {"file": f"profiles/{name}", "per_step": float(d.get("fp64_thread_inst", 0.0)), "per_family": fam}
-    return None
+# evals per step of the runs the committed counter files were captured on (tools/one_step.py)
+PROFILE_EVALS = {"ibmpg2_shaped": 7334331 * 100, "synthetic_ragged": 14743384 * 256, "long_lines": 524288 * 1000}
+
+
+def fp64_counters(workload, evals):
+    """Executed FP64 thread-instructions per step and per kernel family, from the committed ncu launch list of one step
+    of this workload (tools/one_step.py -> tools/launch_summary.py --json), scaled by evals when the run is a larger
+    or smaller instance of the same length mix.  None when no counter file exists for the workload."""
+    p = REPO / "profiles" / f"r02_fp64_counters_{workload}.json"
+    if not p.exists() or workload not in PROFILE_EVALS:
+        return None
+    d = json.loads(p.read_text())
+    scale = float(evals) / PROFILE_EVALS[workload]
+    fam = {}
+    for k, v in d.get("kernels", {}).items():
+        fam.setdefault(kernel_family(k), 0.0)
+        fam[kernel_family(k)] += scale * (v.get("dadd", 0.0) + v.get("dmul", 0.0) + v.get("dfma", 0.0))
+    return {"file": f"profiles/{p.name}", "per_step": scale * float(d.get("fp64_thread_inst", 0.0)), "per_family": fam,
+            "scaled_by": scale}
 
 
 def kernel_family(ncu_name: str) -> str:
@@ -645,7 +651,7 @@ def build_roofline(args, ctx, shard, batch, T, ms_rank, barrier, W):
     ctx.profile(False)
     prof = {k: v for k, v in ctx.profile_read().items() if v[1] > 0}
     tot_ms = sum(v[0] for v in prof.values()) or 1.0
-    counters = fp64_counters(args.workload)
+    counters = fp64_counters(args.workload, evals_rank)
     kernels = {}
     for k, v in prof.items():
         kernels[k] = {"ms_per_step": v[0] / n_prof, "launches_per_step": v[1] / n_prof, "avg_launch_us": 1e3 * v[0] / v[1],

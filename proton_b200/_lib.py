@@ -3,6 +3,7 @@ missing or no GPU is usable, every call fails loudly."""
 from __future__ import annotations
 
 import ctypes
+import os
 from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
@@ -54,17 +55,19 @@ def load() -> ctypes.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not LIB_PATH.exists():
-        raise ProtonEmError(ECUDA, f"{LIB_PATH} is not built (run `python -m proton_b200.build`); "
+    path = Path(os.environ.get("PROTON_EM_LIB", LIB_PATH))      # (override: A/B timing of two builds on one box)
+    if not path.exists():
+        raise ProtonEmError(ECUDA, f"{path} is not built (run `python -m proton_b200.build`); "
                                    "there is no CPU fallback")
-    lib = ctypes.CDLL(str(LIB_PATH))
+    lib = ctypes.CDLL(str(path))
     vp = ctypes.c_void_p
     lib.proton_em_create.argtypes = [ctypes.POINTER(vp), ctypes.c_int]
     lib.proton_em_destroy.argtypes = [vp]
     lib.proton_em_last_error.restype = ctypes.c_char_p
     lib.proton_em_version.restype = ctypes.c_char_p
     lib.proton_em_pack.argtypes = [vp, ctypes.POINTER(Batch), ctypes.c_int, ctypes.POINTER(vp)]
-    lib.proton_em_pack_sigma0.argtypes = [vp, ctypes.POINTER(Batch), vp, ctypes.c_int, ctypes.POINTER(vp)]
+    if hasattr(lib, "proton_em_pack_sigma0"):
+        lib.proton_em_pack_sigma0.argtypes = [vp, ctypes.POINTER(Batch), vp, ctypes.c_int, ctypes.POINTER(vp)]
     lib.proton_em_plan_destroy.argtypes = [vp]
     for f in (lib.proton_em_plan_total_nodes, lib.proton_em_plan_num_lines, lib.proton_em_plan_scratch_bytes,
               lib.proton_em_launch_count):
@@ -86,8 +89,9 @@ def load() -> ctypes.CDLL:
     lib.proton_em_profile.argtypes = [vp, ctypes.c_int]
     lib.proton_em_profile_read.argtypes = [vp, ctypes.c_int, ctypes.POINTER(ctypes.c_char_p),
                                            ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int64)]
-    lib.proton_em_debug_line_table.argtypes = [vp, ctypes.c_int64, ctypes.c_int, vp, ctypes.c_int64,
-                                               ctypes.POINTER(ctypes.c_int64)]
+    if hasattr(lib, "proton_em_debug_line_table"):
+        lib.proton_em_debug_line_table.argtypes = [vp, ctypes.c_int64, ctypes.c_int, vp, ctypes.c_int64,
+                                                   ctypes.POINTER(ctypes.c_int64)]
     _lib = lib
     return lib
 

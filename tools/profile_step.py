@@ -40,7 +40,10 @@ def main():
         from proton_b200.workloads import synthetic_ragged
         batch, desc = None, {"T": args.T}
     else:
-        batch, T0 = bench.build_global(args.workload)
+        if args.workload == "synthetic_ragged20k":
+            batch, T0 = bench.build_global("synthetic_ragged", 20000)
+        else:
+            batch, T0 = bench.build_global(args.workload)
         desc = {"T": T0}
     T = desc["T"]
     ts = bench.timestamps(T)
