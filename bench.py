@@ -634,7 +634,7 @@ def build_roofline(args, ctx, shard, batch, T, ms_rank, barrier, W):
     long_ev = ev_kind.get("long_blue", 0.0) + ev_kind.get("long_pow2", 0.0)
     long_fl = fl_kind.get("long_blue", 0.0) + fl_kind.get("long_pow2", 0.0)
     through = {"em_eval_dense_kernel": ("dense", 1.0), "em_eval_fft_kernel<pow2>": ("fft_pow2", 1.0),
-               "em_eval_fft_kernel<bluestein>": ("fft_blue", 1.0)}
+               "em_eval_fft_kernel<bluestein>": ("fft_blue", 1.0), "em_eval_mix_kernel": ("fft_mix", 1.0)}
     evals_through = {k: ev_kind.get(c, 0.0) for k, (c, _) in through.items()}
     flops_through = {k: fl_kind.get(c, 0.0) for k, (c, _) in through.items()}
     for k in ("em_long_colfwd_paired_kernel", "em_long_row_kernel", "em_long_colinv_kernel", "em_long_scatter_kernel",

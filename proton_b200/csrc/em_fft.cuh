@@ -34,6 +34,7 @@ struct NTab {
   int log2p;            // FFT length class (0 = not on the in-CTA FFT path)
   int bluestein;
   int p1;               // long classes: rows of 4096 points per transform (0 otherwise)
+  int mix;              // mixed-radix in-CTA classes: mix_code(LR, ODD) (0 otherwise; em_mix.cuh)
 };
 
 struct EvalParams {

@@ -4,7 +4,8 @@
 // resident in HBM) and the launch logic that routes each line to a kernel by its length:
 //   N <= 88 (not 64)             em_eval_dense_kernel<MT>       (DMMA contraction with the N x N cosine matrix)
 //   N = 2^p, 64..8192            em_eval_fft_kernel<p, false>   (in-CTA DIT FFT, radix 16/8/4/2)
-//   other N <= 4096              em_eval_fft_kernel<p, true>    (Bluestein, P = 2^p >= 2N-1)
+//   other N <= 4096              em_eval_fft_kernel<p, true>    (Bluestein, P = 2^p >= 2N-1), or
+//                                em_eval_mix_kernel<LR, ROWS>   (Bluestein, P = 5 or 6 x 2^LR when that is shorter)
 //   other N <= 65536, 2^p <= 131072   em_long_{colfwd_paired | scatter} -> em_long_row -> em_long_colinv
 //                                (P = P1 x 4096 through an L2-resident scratch, waves dealt to `lanes` streams)
 // Tuning knobs, all optional environment variables read once: PROTON_EM_LANES (2), PROTON_EM_LONG_WAVE_MB (32),
@@ -32,6 +33,7 @@
 
 #include "em_kernels.cuh"
 #include "em_long.cuh"
+#include "em_mix.cuh"
 
 namespace {
 
@@ -87,7 +89,7 @@ static_assert(sizeof(kLongP1Gevals) / sizeof(double) == sizeof(kLongP1List) / si
 constexpr int kMaxLongPow2N = em::kLongP2 * em::kLongMaxP1;                 // 131072
 constexpr int kMaxLongBlueN = (em::kLongP2 * em::kLongMaxP1) / 2;           // 65536: 2N-1 <= 131072
 
-enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_LPOW2 = 3, CLS_LBLUE = 4, CLS_NONE = 5 };
+enum LineClass { CLS_SMALL = 0, CLS_POW2 = 1, CLS_BLUE = 2, CLS_LPOW2 = 3, CLS_LBLUE = 4, CLS_MIX = 5, CLS_NONE = 6 };
 
 // log2p = log2 of the FFT length for the in-CTA classes; for the long classes it holds P1 (rows of 4096 points).
 struct ClassOf { LineClass cls; int log2p; };
@@ -129,8 +131,24 @@ ClassOf classify(int N) {
   }
   int p = 0;
   while ((1LL << p) < 2LL * N - 1) ++p;
+  // mixed-radix lengths 1.25 and 1.5 x 2^k (em_mix.cuh) when they are shorter than the power of two; PROTON_EM_MIX=0
+  // keeps the power-of-two lengths (for A/B runs)
+  static const bool use_mix = [] { const char* e = std::getenv("PROTON_EM_MIX"); return !(e && std::atoi(e) == 0); }();
+  if (use_mix) {
+    const long long need = 2LL * N - 1;
+    long long best = 1LL << p;
+    int code = 0;
+    for (int lr = 7; lr <= 10; ++lr)
+      for (int odd : {5, 6}) {                                 // rows of 2^lr points
+        const long long P = (long long)odd << lr;
+        if (P >= need && P < best) { best = P; code = em::mix_code(lr, odd); }
+      }
+    if (code) return {CLS_MIX, code};
+  }
   return {CLS_BLUE, p};
 }
+inline int mix_lr(int code) { return code / 8 + 7; }
+inline int mix_odd(int code) { return code % 8; }
 
 // Bump allocator for the per-length tables (lives as long as the context).
 struct Arena {
@@ -224,6 +242,7 @@ struct proton_em_ctx {
   int64_t launches = 0;
   // long-line path: column twiddles per P1 and the wave scratch (grown on demand, reused by every call)
   em::cplx* d_twl[em::kLongMaxP1 + 1] = {};   // column twiddles per P1
+  em::cplx* d_twm[64] = {};                   // column twiddles per mixed class (em_mix.cuh), by mix_code
   static constexpr int kLanes = 8;          // up to 8 streams; `lanes` of them are used (PROTON_EM_LANES, default 2:
                                             // two 32 MB waves in flight measured best, the scratch stays well inside L2)
   int lanes = 2;
@@ -248,10 +267,10 @@ struct proton_em_ctx {
 };
 
 namespace {
-enum ProfKind { PK_DENSE = 0, PK_FFT_POW2, PK_FFT_BLUE, PK_LONG_COLFWD, PK_LONG_ROW, PK_LONG_COLINV,
+enum ProfKind { PK_DENSE = 0, PK_FFT_POW2, PK_FFT_BLUE, PK_FFT_MIX, PK_LONG_COLFWD, PK_LONG_ROW, PK_LONG_COLINV,
                 PK_LONG_SCATTER, PK_LONG_REDUCE, PK_COUNT };
 const char* const kProfNames[PK_COUNT] = {"em_eval_dense_kernel", "em_eval_fft_kernel<pow2>",
-                                          "em_eval_fft_kernel<bluestein>", "em_long_colfwd_paired_kernel",
+                                          "em_eval_fft_kernel<bluestein>", "em_eval_mix_kernel", "em_long_colfwd_paired_kernel",
                                           "em_long_row_kernel", "em_long_colinv_kernel", "em_long_scatter_kernel",
                                           "em_long_reduce_kernel"};
 // Records an event before and after one launch on the stream it is launched on (only while profiling is on).
@@ -368,6 +387,66 @@ int launch_eval_fft(proton_em_ctx* ctx, cudaStream_t st, bool blue, int log2p, c
 #undef M
     default: return fail(PROTON_EM_EINVAL, "bad log2p %d", log2p);
   }
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+#define FOR_EACH_MIX(M) M(7, 5) M(8, 5) M(9, 5) M(10, 5) M(7, 6) M(8, 6) M(9, 6) M(10, 6)
+
+int init_mix_attrs() {
+#define M(lr, odd)                                                                                                    \
+  CU_TRY(cudaFuncSetAttribute(em::em_eval_mix_kernel<lr, odd>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
+                              (int)em::MixCfg<lr, odd>::smem_bytes));                                                 \
+  CU_TRY(cudaFuncSetAttribute(em::em_tables_mix_kernel<lr, odd>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
+                              (int)em::MixCfg<lr, odd>::smem_bytes));
+  FOR_EACH_MIX(M)
+#undef M
+  return PROTON_EM_OK;
+}
+
+// column twiddles w_P^{+j}, j < R, of a mixed class (built at first use, on the context stream)
+int ensure_mix(proton_em_ctx* ctx, int code) {
+  if (ctx->d_twm[code]) return PROTON_EM_OK;
+  const int lr = mix_lr(code), odd = mix_odd(code), R = 1 << lr;
+  CU_TRY(cudaMalloc(reinterpret_cast<void**>(&ctx->d_twm[code]), (size_t)R * sizeof(em::cplx)));
+  em::em_mix_twiddle_kernel<<<(R + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_twm[code], R, odd * R);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int launch_tables_mix(proton_em_ctx* ctx, int code, const em::NTab* d_entries, int count) {
+  { int rc = ensure_mix(ctx, code); if (rc) return rc; }
+  const int lr = mix_lr(code), odd = mix_odd(code);
+  em::TableParams tp{d_entries, ctx->d_tw[lr]};
+  bool done = false;
+#define M(l, o)                                                                                                       \
+  if (lr == l && odd == o) {                                                                                          \
+    em::em_tables_mix_kernel<l, o><<<count, em::MixCfg<l, o>::NT, em::MixCfg<l, o>::smem_bytes, ctx->stream>>>(tp, ctx->d_twm[code]); \
+    done = true;                                                                                                      \
+  }
+  FOR_EACH_MIX(M)
+#undef M
+  if (!done) return fail(PROTON_EM_EINVAL, "bad mixed class %d", code);
+  ctx->launches++;
+  CU_TRY(cudaGetLastError());
+  return PROTON_EM_OK;
+}
+
+int launch_eval_mix(proton_em_ctx* ctx, cudaStream_t st, int code, const em::EvalParams& ep, int grid) {
+  ProfScope prof(ctx, PK_FFT_MIX, st);
+  const int lr = mix_lr(code), odd = mix_odd(code);
+  em::MixParams mp{ep, ctx->d_twm[code]};
+  bool done = false;
+#define M(l, o)                                                                                                       \
+  if (lr == l && odd == o) {                                                                                          \
+    em::em_eval_mix_kernel<l, o><<<grid, em::MixCfg<l, o>::NT, em::MixCfg<l, o>::smem_bytes, st>>>(mp);               \
+    done = true;                                                                                                      \
+  }
+  FOR_EACH_MIX(M)
+#undef M
+  if (!done) return fail(PROTON_EM_EINVAL, "bad mixed class %d", code);
   ctx->launches++;
   CU_TRY(cudaGetLastError());
   return PROTON_EM_OK;
@@ -579,8 +658,9 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
       const ClassOf c = classify(N);
       const size_t nb = ((size_t)N * sizeof(em::cplx) + 255) & ~size_t(255);
       if (c.cls != CLS_SMALL) need += nb;
-      if (c.cls == CLS_BLUE || c.cls == CLS_LBLUE) {
-        const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2 : ((size_t)1 << c.log2p);
+      if (c.cls == CLS_BLUE || c.cls == CLS_LBLUE || c.cls == CLS_MIX) {
+        const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2
+                          : c.cls == CLS_MIX ? ((size_t)mix_odd(c.log2p) << mix_lr(c.log2p)) : ((size_t)1 << c.log2p);
         need += nb + ((plen * sizeof(em::cplx) + 255) & ~size_t(255));
       }
     }
@@ -600,16 +680,19 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
     t.bluestein = c.cls == CLS_BLUE;
     t.p1 = 0;
     if (c.cls == CLS_LPOW2 || c.cls == CLS_LBLUE) { t.p1 = c.log2p; t.bluestein = c.cls == CLS_LBLUE; }
+    t.mix = c.cls == CLS_MIX ? c.log2p : 0;
+    if (c.cls == CLS_MIX) t.bluestein = 1;
     if (c.cls != CLS_SMALL) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
       t.pre = static_cast<const em::cplx*>(p);
     }
-    if (c.cls == CLS_BLUE || c.cls == CLS_LBLUE) {
+    if (c.cls == CLS_BLUE || c.cls == CLS_LBLUE || c.cls == CLS_MIX) {
       void* p = nullptr;
       CU_TRY(ctx->arena.alloc(&p, (size_t)N * sizeof(em::cplx)));
       t.post = static_cast<const em::cplx*>(p);
-      const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2 : ((size_t)1 << c.log2p);
+      const size_t plen = c.cls == CLS_LBLUE ? (size_t)c.log2p * em::kLongP2
+                        : c.cls == CLS_MIX ? ((size_t)mix_odd(c.log2p) << mix_lr(c.log2p)) : ((size_t)1 << c.log2p);
       CU_TRY(ctx->arena.alloc(&p, plen * sizeof(em::cplx)));
       t.hhat = static_cast<const em::cplx*>(p);
     }
@@ -620,13 +703,19 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
   // and without host synchronisation in between.
   std::vector<em::NTab> sorted;
   sorted.reserve(entries.size());
-  struct Group { int blue, key; size_t off, cnt; bool is_long; };
+  struct Group { int blue, key; size_t off, cnt; bool is_long; bool is_mix = false; };
   std::vector<Group> groups;
+  for (int code = 1; code < 64; ++code) {
+    const size_t off = sorted.size();
+    for (const em::NTab& t : entries)
+      if (t.mix == code) sorted.push_back(t);
+    if (sorted.size() > off) { Group g{1, code, off, sorted.size() - off, false}; g.is_mix = true; groups.push_back(g); }
+  }
   for (int blue = 0; blue < 2; ++blue)
     for (int p = kMinLog2P; p <= kMaxLog2P; ++p) {
       const size_t off = sorted.size();
       for (const em::NTab& t : entries)
-        if (t.log2p == p && t.bluestein == blue) sorted.push_back(t);
+        if (t.log2p == p && t.bluestein == blue && t.mix == 0) sorted.push_back(t);
       if (sorted.size() > off) groups.push_back({blue, p, off, sorted.size() - off, false});
     }
   for (int blue = 0; blue < 2; ++blue)
@@ -643,7 +732,8 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
     CU_TRY(cudaMemcpyAsync(d_sorted, sorted.data(), sorted.size() * sizeof(em::NTab), cudaMemcpyHostToDevice, ctx->stream));
     for (const Group& g : groups) {
       int rc;
-      if (g.is_long) rc = long_build_tables(ctx, d_sorted + g.off, (int)g.cnt, g.key, g.blue != 0);
+      if (g.is_mix) rc = launch_tables_mix(ctx, g.key, d_sorted + g.off, (int)g.cnt);
+      else if (g.is_long) rc = long_build_tables(ctx, d_sorted + g.off, (int)g.cnt, g.key, g.blue != 0);
       else rc = g.blue ? launch_tables<true>(ctx, g.key, d_sorted + g.off, (int)g.cnt)
                        : launch_tables<false>(ctx, g.key, d_sorted + g.off, (int)g.cnt);
       if (rc) { cudaStreamSynchronize(ctx->stream); return rc; }
@@ -779,6 +869,7 @@ int proton_em_create(proton_em_ctx** out, int device) {
   }
   int rc = init_kernel_attrs();
   if (rc == PROTON_EM_OK) rc = init_long_attrs();
+  if (rc == PROTON_EM_OK) rc = init_mix_attrs();
   if (rc == PROTON_EM_OK) {
     const int n = em::kDenseMaxN;
     const cudaError_t e = cudaFuncSetAttribute(em::em_eval_dense_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -815,6 +906,7 @@ int proton_em_destroy(proton_em_ctx* ctx) {
   for (auto* p : ctx->d_tw) if (p) cudaFree(p);
   for (auto* p : ctx->d_pos) if (p) cudaFree(p);
   for (auto* p : ctx->d_twl) if (p) cudaFree(p);
+  for (auto* p : ctx->d_twm) if (p) cudaFree(p);
   ctx->long_x.free(); ctx->long_y.free(); ctx->long_part_v.free(); ctx->long_part_i.free();
   ctx->arena.release();
   if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
@@ -1320,6 +1412,21 @@ static int eval_device_core(proton_em_plan* p, const double* d_ts, int T, const 
         }
         continue;
       }
+    }
+    if (cl.cls == CLS_MIX) {
+      // one transform at a time per CTA; the timestamp pairs of a line are cut into chunks until the grid is large enough
+      const int npairs = (T + 1) / 2;
+      int chunks = (int)std::min<long long>(npairs, std::max<long long>(1, (target_items + cl.count - 1) / cl.count));
+      const int ppc = (npairs + chunks - 1) / chunks;
+      chunks = (npairs + ppc - 1) / ppc;
+      em::EvalParams ep{p->d_class_lines.p + cl.offset, cl.count, chunks, ppc, T, p->d_num_nodes, p->d_a,
+                        p->d_node_off.p, p->d_line_tab.p, p->d_tabs.p, p->d_W.p, d_ts, ctx->d_tw[mix_lr(cl.log2p)],
+                        nullptr, d_stress, d_mx, d_amx, d_flag, critical};
+      const long long grid = (long long)cl.count * chunks;
+      if (grid > 0x7fffffffLL) return fail(PROTON_EM_EINVAL, "too many work items");
+      int rc = launch_eval_mix(ctx, cst, cl.log2p, ep, (int)grid);
+      if (rc) return rc;
+      continue;
     }
     const bool blue = cl.cls == CLS_BLUE;
     const int G = fft_group(blue, cl.log2p);

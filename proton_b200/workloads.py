@@ -191,7 +191,12 @@ def kernel_class(n: int, dense_max: int = 88) -> str:
         return "dense"
     if pow2:
         return "fft_pow2" if n <= 8192 else "long_pow2"
-    return "fft_blue" if n <= 4096 else "long_blue"
+    if n > 4096:
+        return "long_blue"
+    need = 2 * n - 1
+    p2 = 1 << (need - 1).bit_length()
+    mixed = [rows << lr for lr in range(7, 11) for rows in (5, 6)]
+    return "fft_mix" if any(need <= P < p2 for P in mixed) else "fft_blue"
 
 
 def partition_lines(num_nodes: np.ndarray, world: int, T: int = 1) -> List[np.ndarray]:

@@ -81,11 +81,14 @@ def test_gpu_initial_stress_against_the_oracle_all_length_classes(oracle):
 
 
 @pytest.mark.gpu
-def test_restart_from_the_evaluated_field_equals_the_current_history():
+def test_restart_from_the_evaluated_field_equals_the_current_history(oracle):
     """proton_em_analyze_history_host (superposition of current increments) re-expressed as restarts: evaluate to the
-    switching time, hand the field back as sigma0 with the next currents, continue.  The two routes share no forward
-    transform (sparse sums of the current increments vs dense DCT-II of the restart field); measured agreement on B200:
-    1.7e-12 norm-wise after two restarts, asserted at 1e-11."""
+    switching time, hand the field back as sigma0 with the next currents, continue.
+    Two statements.  (i) The GPU restart equals the CPU oracle's restart from the same field to rounding (1e-12).
+    (ii) Restart and superposition agree to 1e-9: they are the same mathematics, but they call the reference's closed
+    form at different times (t and t - tau), and that form loses digits through exp(x) - 1.0 (SURVEY.md F10,
+    tests/test_truth.py) — the CPU oracles of the two routes differ from each other by the same 7.5e-11 (N = 3000) that
+    the GPU routes do, measured on B200."""
     from proton_b200.api import Context
     rng = np.random.default_rng(51)
     batch = synth_batch(rng, [5, 40, 64, 300, 1000, 3000, 5000, 9000])
@@ -94,25 +97,33 @@ def test_restart_from_the_evaluated_field_equals_the_current_history():
     u3 = 0.25 * u1
     tau = np.array([0.0, 2.0e7, 2.0e8])
     ts = np.array([2.5e7, 1.9e8, 2.0e8, 3.0e8, 6.38e8])
+    T = len(ts)
+    off = batch.node_off
+    args = (batch.num_nodes, batch.a_coeff, batch.trip_off, batch.trip_row, batch.trip_col, batch.trip_val, batch.u_off)
     ctx = Context(0)
     try:
         hist = ctx.analyze_history(batch, [u1, u2, u3], tau, ts, critical=40e6)
-        # segment 1 from zero to tau_1
-        f1 = ctx.pack(batch).eval(np.array([tau[1]])).stress
-        b2 = LineBatch(batch.num_nodes, batch.a_coeff, batch.trip_off, batch.trip_row, batch.trip_col, batch.trip_val,
-                       batch.u_off, u2)
+        f1 = ctx.pack(batch).eval(np.array([tau[1]])).stress              # segment 1 from zero to tau_1
+        b2 = LineBatch(*args, u2)
         p2 = ctx.pack(b2, sigma0=f1)
         in2 = ts <= tau[2]
         r2 = p2.eval(ts[in2] - tau[1], critical=40e6)
         f2 = p2.eval(np.array([tau[2] - tau[1]])).stress
-        b3 = LineBatch(batch.num_nodes, batch.a_coeff, batch.trip_off, batch.trip_row, batch.trip_col, batch.trip_val,
-                       batch.u_off, u3)
-        r3 = ctx.pack(b3, sigma0=f2).eval(ts[~in2] - tau[2], critical=40e6)
+        r3 = ctx.pack(LineBatch(*args, u3), sigma0=f2).eval(ts[~in2] - tau[2], critical=40e6)
+        o2, _, _ = oracle.sigma0_batch(*args, u2, f1, ts[in2] - tau[1])
+        o3, _, _ = oracle.sigma0_batch(*args, u3, f2, ts[~in2] - tau[2])
+        T2, T3 = int(in2.sum()), int((~in2).sum())
+        worst_restart = worst_routes = 0.0
         for l in range(batch.num_lines):
+            n = int(batch.num_nodes[l])
             want = hist.line(l)
             got = np.concatenate([r2.line(l), r3.line(l)])
+            orc = np.concatenate([o2[off[l] * T2:off[l + 1] * T2].reshape(T2, n), o3[off[l] * T3:off[l + 1] * T3].reshape(T3, n)])
             scale = np.abs(want).max(axis=1)
-            err = np.abs(got - want).max(axis=1) / scale
-            assert err.max() < 1e-11, (l, err)
+            worst_restart = max(worst_restart, float((np.abs(got - orc).max(axis=1) / scale).max()))
+            worst_routes = max(worst_routes, float((np.abs(got - want).max(axis=1) / scale).max()))
+        print(f"restart: GPU vs oracle restart {worst_restart:.2e}; restart vs superposition {worst_routes:.2e}")
+        assert worst_restart < 1e-12
+        assert worst_routes < 1e-9
     finally:
         ctx.close()
