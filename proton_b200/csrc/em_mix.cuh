@@ -2,8 +2,9 @@
 //
 // em_eval_fft_kernel<p, true> pads every line to the next power of two P >= 2N-1, so a line just above a power of two
 // does twice the necessary transform length.  With the lengths 1.25 and 1.5 x 2^k in between, the average excess over
-// 2N drops from 44 % to 17 % for line lengths spread evenly in log N, and the longest in-CTA lines (2049..3072 nodes)
-// need 5120 or 6144 points instead of 8192.
+// 2N drops from 44 % to 17 % for line lengths spread evenly in log N, and lines of 2049..3072 nodes need 5120 or 6144
+// points instead of 8192 — two CTAs per SM instead of one.  Measured on B200 (T = 256): +24..47 % on the lengths that
+// change class, synthetic ragged batch 66.0 -> 57.7 ms per step.
 //
 // Structure: the long path's three passes (em_long.cuh) inside one CTA, with shared memory in place of the L2 scratch.
 // The P points are ODD rows of R = 2^LR points, element index i = j + q R (row q, column j):
@@ -22,11 +23,14 @@
 namespace em {
 
 // Row counts: 5 (P = 1.25 x 2^k) and 6 (P = 1.5 x 2^k, as six half-length rows rather than three: an even row count
-// splits evenly over the two row groups a CTA works on at a time, and 6 x 1024 points leave room for two CTAs per SM
-// where 3 x 2048 do not).  Threads: twice the butterflies of one row stage, so two rows are in work at a time.
+// splits evenly over the row groups a CTA works on at a time, and 6 x 1024 points leave room for two CTAs per SM
+// where 3 x 2048 do not: measured 63 vs 42 Gevals/s at N = 3000).
 template <int LR, int ODD> struct MixCfg {
   static constexpr int R = 1 << LR, P = ODD * R;
-  static constexpr int NT = LR >= 10 ? 256 : LR == 9 ? 128 : 64;
+  static constexpr int NT = LR >= 10 ? 256 : LR >= 8 ? 128 : 64;
+  // resident CTAs the register budget is sized for: 512 threads per SM for the long rows (128 registers; shared memory
+  // allows no more CTAs anyway), 768 for the short ones (80 registers: measured +3..13 % there, neutral for LR = 9)
+  static constexpr int MINB = (LR >= 9 ? 512 : 768) / NT;
   static constexpr int RSTRIDE = padded_len<LR>();                    // padded row length (complex elements)
   static constexpr size_t tw_bytes = (size_t)stage_tw_total(LR) * sizeof(cplx);
   static constexpr size_t smem_bytes = tw_bytes + (size_t)ODD * RSTRIDE * sizeof(cplx);
@@ -85,7 +89,7 @@ struct MixParams {
 };
 
 template <int LR, int ODD>
-__global__ void __launch_bounds__(MixCfg<LR, ODD>::NT, 512 / MixCfg<LR, ODD>::NT) em_eval_mix_kernel(const MixParams mp) {
+__global__ void __launch_bounds__(MixCfg<LR, ODD>::NT, MixCfg<LR, ODD>::MINB) em_eval_mix_kernel(const MixParams mp) {
   using C = MixCfg<LR, ODD>;
   constexpr int R = C::R, NT = C::NT, RS = C::RSTRIDE, NST = plan_n(LR), QN = C::QN;
   const EvalParams& prm = mp.e;

@@ -25,7 +25,7 @@ def main():
     if args.uniform:
         b, T = synthetic_ragged(0, seed=1, sizes=[args.uniform] * args.lines), args.T
     else:
-        b, T = bench.build_global(args.workload)
+        b, T = bench.build_global(args.workload, 20000 if args.workload == "synthetic_ragged" else 0)
     ctx = Context(0)
     dev = torch.device("cuda:0")
     sh = bench.Shard(ctx, torch, dev, b, T)
