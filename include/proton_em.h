@@ -182,7 +182,8 @@ int proton_em_debug_expm1(proton_em_ctx* ctx, const double* x_host, double* y_ho
 /* Test hook for the CPU twin of the GPU arithmetic (oracle/em_twin.c, tests/test_twin.py): copies one of the tables
  * the kernels read for `line` of a packed plan to host memory.  which: 0 lambda_k [N]; 1 modal weights W_k [N];
  * 2 pre-twiddles [N complex = 2N doubles]; 3 Bluestein post-chirp [2N doubles]; 4 the cosine table of the short-line
- * kernel, cos(pi m / 2N), m < 4N.  `count` receives the number of doubles. */
+ * kernel, cos(pi m / 2N), m < 4N; 5 the transformed chirp H of a Bluestein class [P complex]; 6 the column twiddles
+ * w_P^{+j} of a mixed-radix or long class [row length, complex].  `count` receives the number of doubles. */
 int proton_em_debug_line_table(proton_em_plan* plan, int64_t line, int which, double* out, int64_t capacity, int64_t* count);
 
 #ifdef __cplusplus

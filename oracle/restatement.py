@@ -283,6 +283,11 @@ def load_twin() -> ctypes.CDLL:
         for f in (lib.em_twin_dense, lib.em_twin_pow2):
             f.argtypes = [ctypes.c_int, ctypes.c_double, c_dp, c_dp, c_dp, ctypes.c_int, c_dp, c_dp]
             f.restype = ctypes.c_int
+        lib.em_twin_blue.argtypes = [ctypes.c_int, ctypes.c_double, c_dp, c_dp, c_dp, c_dp, c_dp, ctypes.c_int, c_dp, c_dp]
+        lib.em_twin_blue.restype = ctypes.c_int
+        lib.em_twin_rows.argtypes = [ctypes.c_int, ctypes.c_double, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, ctypes.c_int,
+                                     ctypes.c_int, ctypes.c_int, ctypes.c_int, c_dp, c_dp]
+        lib.em_twin_rows.restype = ctypes.c_int
         _twin = lib
     return _twin
 
@@ -299,4 +304,24 @@ def twin_line(kind: str, N: int, a: float, lam, W, table, ts) -> np.ndarray:
     rc = fn(int(N), float(a), _dp(lam), _dp(W), _dp(table), len(ts), _dp(ts), _dp(out))
     if rc:
         raise ValueError(f"em_twin_{kind} rc={rc}")
+    return out
+
+
+def twin_bluestein(N: int, a: float, lam, W, pre, post, hhat, ts, twl=None, lr: int = 0, rows: int = 0,
+                   long_path: bool = False) -> np.ndarray:
+    """Stress [T, N] of one line exactly as a Bluestein class of the GPU computes it: the in-CTA power-of-two class
+    (rows == 0), a mixed-radix class (rows x 2^lr points) or the long path (rows = P1, lr = 12, long_path=True), from the
+    device's own tables."""
+    c = lambda x: np.ascontiguousarray(x, dtype=np.float64)
+    lam, W, pre, post, hhat, ts = c(lam), c(W), c(pre), c(post), c(hhat), c(np.atleast_1d(ts))
+    out = np.empty((len(ts), N), dtype=np.float64)
+    if rows == 0:
+        rc = load_twin().em_twin_blue(int(N), float(a), _dp(lam), _dp(W), _dp(pre), _dp(post), _dp(hhat), len(ts), _dp(ts),
+                                      _dp(out))
+    else:
+        twl = c(twl)
+        rc = load_twin().em_twin_rows(int(N), float(a), _dp(lam), _dp(W), _dp(pre), _dp(post), _dp(hhat), _dp(twl), int(lr),
+                                      int(rows), int(bool(long_path)), len(ts), _dp(ts), _dp(out))
+    if rc:
+        raise ValueError(f"em_twin bluestein rc={rc}")
     return out

@@ -288,12 +288,12 @@ class Plan:
         except Exception:
             pass
 
-    TABLES = {"lambda": 0, "W": 1, "pre": 2, "post": 3, "costab": 4}
+    TABLES = {"lambda": 0, "W": 1, "pre": 2, "post": 3, "costab": 4, "hhat": 5, "twl": 6}
 
     def debug_table(self, line: int, which: str) -> np.ndarray:
         """Test hook: one of the device tables the kernels read for `line` (float64; complex tables interleaved)."""
         N = int(self.node_off[line + 1] - self.node_off[line])
-        out = np.empty(4 * N + 8, dtype=np.float64)
+        out = np.empty(max(4 * N + 8, 2 * 131072 + 8), dtype=np.float64)
         n = ctypes.c_int64()
         check(self.ctx._lib.proton_em_debug_line_table(self._h, int(line), self.TABLES[which], out.ctypes.data, out.size,
                                                        ctypes.byref(n)))

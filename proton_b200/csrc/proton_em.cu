@@ -1664,6 +1664,19 @@ int proton_em_debug_line_table(proton_em_plan* p, int64_t line, int which, doubl
     case 2: src = t.pre; n = t.pre ? 2LL * N : 0; break;
     case 3: src = t.post; n = t.post ? 2LL * N : 0; break;
     case 4: n = 4LL * N; break;
+    case 5: {                                     // transformed chirp H: P complex values of the line's class
+      const ClassOf c = classify(N);
+      const long long P = c.cls == CLS_BLUE ? (1LL << c.log2p) : c.cls == CLS_LBLUE ? (long long)c.log2p * em::kLongP2
+                        : c.cls == CLS_MIX ? ((long long)mix_odd(c.log2p) << mix_lr(c.log2p)) : 0;
+      src = t.hhat; n = t.hhat ? 2 * P : 0;
+      break;
+    }
+    case 6: {                                     // column twiddles w_P^{+j}, j < row length (mixed and long classes)
+      const ClassOf c = classify(N);
+      if (c.cls == CLS_MIX) { src = ctx->d_twm[c.log2p]; n = src ? 2LL << mix_lr(c.log2p) : 0; }
+      else if (c.cls == CLS_LBLUE || c.cls == CLS_LPOW2) { src = ctx->d_twl[c.log2p] ? ctx->d_twl[c.log2p] + em::kLongP2 : nullptr; n = src ? 2LL * em::kLongP2 : 0; }
+      break;
+    }
     default: return fail(PROTON_EM_EINVAL, "unknown table %d", which);
   }
   *count = n;

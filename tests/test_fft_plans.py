@@ -72,3 +72,33 @@ def test_padding_identity_and_bank_conflicts(log2p):
     assert max(worst_conflict([pad(log2p, digit_pos(log2p, k)) for k in range(k0, k0 + 32)]) for k0 in range(0, P, 32)) == 1
     assert max(worst_conflict([pad(log2p, k) for k in range(k0, k0 + 32)]) for k0 in range(0, P, 32)) == 1
     assert pad(log2p, P - 1) + 1 <= ((pad(log2p, P - 1) + 8) & ~7)      # padded_len()
+
+
+def padded_len(log2p):
+    return (pad(log2p, (1 << log2p) - 1) + 8) & ~7
+
+
+@pytest.mark.parametrize("lr,rows", [(lr, rows) for lr in range(7, 11) for rows in (5, 6)])
+def test_mixed_radix_rows_layout_and_choice(lr, rows):
+    """em_mix.cuh: P = rows x 2^lr points as `rows` padded rows.  The column passes read and write element
+    (row q, column j) for consecutive j per lane — conflict-free because a row's padding is conflict-free in natural order
+    and the row stride is a multiple of 8 elements — and the rows fit the shared memory the kernel asks for (two CTAs per
+    SM for the 5120- and 6144-point classes).  The host's choice of class (classify() in csrc/proton_em.cu, mirrored by
+    workloads.kernel_class) picks the shortest admissible length."""
+    from proton_b200.workloads import kernel_class
+    R, rs = 1 << lr, padded_len(lr)
+    assert rs % 8 == 0
+    for q in range(rows):
+        assert max(worst_conflict([q * rs + pad(lr, j) for j in range(j0, j0 + 32)]) for j0 in range(0, R, 32)) == 1
+    tw = sum((1 << (lr - sum(lg2(r) for r in plan(lr)[:i + 1]))) for i in range(len(plan(lr)))
+             if lr - sum(lg2(r) for r in plan(lr)[:i + 1]) > 0)
+    smem = (tw + rows * rs) * 16
+    assert smem <= 227 * 1024
+    if lr == 10:
+        assert 2 * (smem + 192 + 1024) <= 228 * 1024          # two CTAs per SM (1 KB per CTA is reserved by the runtime)
+    P = rows << lr
+    n_max = (P + 1) // 2                                       # 2N - 1 <= P
+    assert kernel_class(n_max) == "fft_mix"
+    lengths = sorted({r << l for l in range(7, 11) for r in (5, 6)} | {1 << p for p in range(7, 14)})
+    prev = max(x for x in lengths if x < P)
+    assert kernel_class((prev + 1) // 2 + 1) == "fft_mix"       # just above the next shorter length: this class

@@ -44,3 +44,71 @@ def test_gpu_field_and_reductions_equal_the_cpu_twin_bit_for_bit(oracle, kind, s
         plan.close()
     finally:
         ctx.close()
+
+
+def _class_of(n):
+    """(kind, lr, rows) of a non-power-of-two line above the dense limit — mirror of classify() in csrc/proton_em.cu."""
+    need = 2 * n - 1
+    if n > 4096:
+        return None                      # long path: the row count comes from the device table (see below)
+    p2 = 1 << (need - 1).bit_length()
+    best = min(((r << lr), lr, r) for lr in range(7, 11) for r in (5, 6) if (r << lr) >= need) if need <= (6 << 10) else None
+    if best and best[0] < p2:
+        return ("mix", best[1], best[2])
+    return ("blue", 0, 0)
+
+
+@pytest.mark.parametrize("sizes", [[100, 129, 200, 255, 400, 511, 777, 1000, 2047, 3500, 4095],          # P = 2^p
+                                   [257, 300, 330, 360, 513, 600, 700, 1025, 1100, 1300, 1500, 2049, 2500, 2600, 3000]])
+def test_bluestein_classes_equal_the_cpu_twin_bit_for_bit(oracle, sizes):
+    """In-CTA Bluestein with power-of-two and with mixed-radix lengths (5 or 6 rows of 2^k points)."""
+    from proton_b200.api import Context
+    rng = np.random.default_rng(8)
+    batch = synth_batch(rng, sizes)
+    ctx = Context(0)
+    try:
+        plan = ctx.pack(batch)
+        got = plan.eval(TS, critical=40e6)
+        kinds = set()
+        for l, n in enumerate(sizes):
+            kind, lr, rows = _class_of(n)
+            kinds.add((kind, lr, rows))
+            t = {k: plan.debug_table(l, k) for k in ("lambda", "W", "pre", "post", "hhat")}
+            twl = plan.debug_table(l, "twl") if kind == "mix" else None
+            want = oracle.twin_bluestein(n, float(batch.a_coeff[l]), t["lambda"], t["W"], t["pre"], t["post"], t["hhat"], TS,
+                                         twl=twl, lr=lr, rows=rows)
+            g = got.line(l)
+            same = g.view(np.uint64) == want.view(np.uint64)
+            assert same.all(), (f"N={n} {kind} lr={lr} rows={rows}: {np.count_nonzero(~same)} of {same.size} values differ, "
+                                f"worst {np.abs(g - want).max() / np.abs(want).max():.3e}")
+            assert np.array_equal(got.max_stress[l], want.max(axis=1)) and np.array_equal(got.argmax[l], want.argmax(axis=1))
+        assert len(kinds) == 1 or len(kinds) >= 6          # the second list goes through six mixed-radix classes
+        plan.close()
+    finally:
+        ctx.close()
+
+
+def test_long_lines_equal_the_cpu_twin_bit_for_bit(oracle):
+    """The three-kernel long path (P = P1 x 4096 through the L2-resident scratch): the headline workload's lines."""
+    from proton_b200.api import Context
+    rng = np.random.default_rng(9)
+    sizes = [4097, 5000, 6145, 9000, 12001, 19087, 25564, 33000, 65535]
+    batch = synth_batch(rng, sizes)
+    ts = TS[:3]
+    ctx = Context(0)
+    try:
+        plan = ctx.pack(batch)
+        got = plan.eval(ts, critical=40e6)
+        for l, n in enumerate(sizes):
+            t = {k: plan.debug_table(l, k) for k in ("lambda", "W", "pre", "post", "hhat", "twl")}
+            p1 = len(t["hhat"]) // (2 * 4096)
+            want = oracle.twin_bluestein(n, float(batch.a_coeff[l]), t["lambda"], t["W"], t["pre"], t["post"], t["hhat"], ts,
+                                         twl=t["twl"], lr=12, rows=p1, long_path=True)
+            g = got.line(l)
+            same = g.view(np.uint64) == want.view(np.uint64)
+            assert same.all(), (f"N={n} P1={p1}: {np.count_nonzero(~same)} of {same.size} values differ, "
+                                f"worst {np.abs(g - want).max() / np.abs(want).max():.3e}")
+            assert np.array_equal(got.max_stress[l], want.max(axis=1)) and np.array_equal(got.argmax[l], want.argmax(axis=1))
+        plan.close()
+    finally:
+        ctx.close()
