@@ -113,21 +113,31 @@ template <int R> __device__ __forceinline__ void col_twiddle(cplx (&v)[R], cplx 
   }
 }
 
+// Everything a long-path kernel needs to know about one transform slot, in one 80-byte record that the host builds
+// once per (plan, T): the kernels used to walk slot -> line -> table index -> table -> pointer -> data, five dependent
+// loads from L2 before the first useful one (24 % of the inverse column kernel's stall samples sat on the post-chirp
+// loads at the end of that chain, profiles/r01_ncu_long_full.txt); now it is slot -> record -> data.
+struct alignas(16) SlotRec {
+  const double* lam;       // lambda_k of the line's length
+  const double* W;         // modal weights of the line
+  const cplx* pre;         // pre-chirp / pre-twiddle
+  const cplx* post;        // post-chirp (Bluestein)
+  const cplx* hhat;        // transformed chirp (Bluestein)
+  long long stress_off;    // node_off[line] * T + 2 * pair * N: first timestamp's row in the stress field
+  int N;
+  int line;
+  int pair;
+  int reserved;
+};
+
 struct LongWave {
-  // transforms of this wave: slot s -> (line, timestamp pair)
-  const int* tr_line;
-  const int* tr_pair;
+  // transforms of this wave: slot s -> record
+  const SlotRec* recs;
   int n_tr;
   int tr_base;           // index of slot 0 among all transforms of the class (partials are per class)
   int T;
-  const int* num_nodes;
   const double* a_coeff;
-  const long long* node_off;
-  const int* line_tab;
-  const NTab* tabs;
-  const double* W;
   const double* ts;
-  const ulonglong2* exp_tab;
   cplx* x;               // [n_tr][P]
   double* stress;
   double* part_v;        // [n_tr][2][colblocks]
@@ -234,8 +244,9 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
   const int s0 = blockIdx.y * p.tr_per_cta;
   const int s1 = min(p.w.n_tr, s0 + p.tr_per_cta);
   for (int s = s0; s < s1; ++s) {
-    const int line = p.w.tr_line[s], pr = p.w.tr_pair[s];
-    const int N = p.w.num_nodes[line];
+    const SlotRec rec = p.w.recs[s];
+    const int line = rec.line, pr = rec.pair;
+    const int N = rec.N;
     const int c = N & (P2 - 1);
     if (c != prev_c) {
       prev_c = c;
@@ -254,8 +265,7 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
         wbase = cplx{t.x, -t.y};
       }
     }
-    const NTab tab = p.w.tabs[p.w.line_tab[line]];
-    const double* W = p.w.W + p.w.node_off[line];
+    const double* W = rec.W;
     const double av = p.w.a_coeff[line];
     const double t1 = p.w.ts[2 * pr];
     const double t2 = (2 * pr + 1 < p.w.T) ? p.w.ts[2 * pr + 1] : t1;
@@ -266,7 +276,7 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
       const int k = j + q * P2;
       yk[q] = cplx{0.0, 0.0};
       if (active && q < P1 && k < N) {
-        const double l = tab.lam[k], wk = W[k];
+        const double l = rec.lam[k], wk = W[k];
         yk[q] = cplx{em_modal(l, wk, w1, t1), em_modal(l, wk, w2, t2)};
       }
       ys[q * 128 + tid] = yk[q];
@@ -283,7 +293,7 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
           cplx ym = cplx{0.0, 0.0};
           if (kk < N) ym = ys[(kk >> kLongLog2P2) * 128 + partner];
           const cplx z = cplx{yk[q].x + ym.y, yk[q].y - ym.x};
-          v[q] = k == 0 ? z : cmul(ldg_cplx(tab.pre + k), z);
+          v[q] = k == 0 ? z : cmul(ldg_cplx(rec.pre + k), z);
         }
       }
     }
@@ -311,12 +321,12 @@ template <int LOG2P1>
 __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) {
   constexpr long long P = (long long)1 << (LOG2P1 + kLongLog2P2);
   const int s = blockIdx.y;
-  const int line = w.tr_line[s];
-  const int N = w.num_nodes[line];
-  const NTab tab = w.tabs[w.line_tab[line]];
-  const double* W = w.W + w.node_off[line];
+  const SlotRec rec = w.recs[s];
+  const int line = rec.line;
+  const int N = rec.N;
+  const double* W = rec.W;
   const double a = w.a_coeff[line];
-  const int pr = w.tr_pair[s];
+  const int pr = rec.pair;
   const double t1 = w.ts[2 * pr];
   const double t2 = (2 * pr + 1 < w.T) ? w.ts[2 * pr + 1] : t1;
   const double w1 = __dmul_rn(a, t1), w2 = __dmul_rn(a, t2);
@@ -324,17 +334,17 @@ __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) 
   pdl_launch_dependents();
   pdl_wait();
   // one thread per mode pair (k, N-k): the four modal values serve both packed entries
-  const double* __restrict__ lam = tab.lam;
+  const double* __restrict__ lam = rec.lam;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; 2 * k <= N; k += gridDim.x * blockDim.x) {
     const double l = lam[k], wk = W[k];
     const double y1 = em_modal(l, wk, w1, t1), y2 = em_modal(l, wk, w2, t2);
     if (k == 0) { x[long_pos<LOG2P1>(0)] = cplx{y1, y2}; continue; }
     const int kk = N - k;
-    if (kk == k) { x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(tab.pre + k), cplx{y1 + y2, y2 - y1}); continue; }
+    if (kk == k) { x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(rec.pre + k), cplx{y1 + y2, y2 - y1}); continue; }
     const double lm = lam[kk], wm = W[kk];
     const double m1 = em_modal(lm, wm, w1, t1), m2 = em_modal(lm, wm, w2, t2);
-    x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(tab.pre + k), cplx{y1 + m2, y2 - m1});
-    x[long_pos<LOG2P1>(kk)] = cmul(ldg_cplx(tab.pre + kk), cplx{m1 + y2, m2 - y1});
+    x[long_pos<LOG2P1>(k)] = cmul(ldg_cplx(rec.pre + k), cplx{y1 + m2, y2 - m1});
+    x[long_pos<LOG2P1>(kk)] = cmul(ldg_cplx(rec.pre + kk), cplx{m1 + y2, m2 - y1});
   }
 }
 
@@ -345,9 +355,7 @@ struct RowParams {
   cplx* x;
   int p1;                  // rows per transform
   int mode;
-  const int* tr_line;
-  const int* line_tab;
-  const NTab* tabs;
+  const SlotRec* recs;     // evaluation: the transform slots of the wave
   const NTab* tabs_build;
   const cplx* tw;          // per-stage twiddle tables of the 4096-point transform
 };
@@ -398,6 +406,7 @@ __global__ void __launch_bounds__(kLongRowThreads, 2) em_long_row_kernel(const R
   for (int i = tid; i < stage_tw_total(LOG2P); i += NT) twb[i] = p.tw[i];
   const long long P = (long long)P2 * p.p1;
   cplx* row = p.x + (long long)s * P + (long long)r * P2;
+  const cplx* hh = (p.mode == 0) ? p.recs[s].hhat + (long long)r * P2 : nullptr;   // (not written by the predecessor)
   pdl_wait();                                         // the row comes from the preceding column / scatter kernel
   if (p.mode != 2) {
     __syncthreads();                                  // twiddles in place
@@ -411,7 +420,6 @@ __global__ void __launch_bounds__(kLongRowThreads, 2) em_long_row_kernel(const R
       for (int i = tid; i < P2; i += NT) out[i] = data[pad_idx<LOG2P>(i)];
       return;
     }
-    const cplx* hh = p.tabs[p.line_tab[p.tr_line[s]]].hhat + (long long)r * P2;
     fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, 1, hh, tid);
     stage_barrier<LOG2P, NST - 2>();
     DitStages<LOG2P, NST - 2, 1, NT>::run(data, 1, twb, tid);
@@ -450,10 +458,10 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
   pdl_wait();                                         // x is the row kernel's output
   const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
   for (int s = s0; s < s1; ++s) {
-    const int line = p.w.tr_line[s], pr = p.w.tr_pair[s];
-    const int N = p.w.num_nodes[line];
+    const SlotRec rec = p.w.recs[s];
+    const int pr = rec.pair;
+    const int N = rec.N;
     const int halfN = (N + 1) >> 1;
-    const NTab tab = p.w.tabs[p.w.line_tab[line]];
     const cplx* x = p.w.x + (long long)s * P;
     cplx v[P1];
 #pragma unroll
@@ -462,7 +470,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
     DftAny<P1, +1>::run(v);
     const int T = p.w.T;
     const int tj1 = 2 * pr, tj2 = 2 * pr + 1;
-    double* d1 = p.w.stress ? p.w.stress + p.w.node_off[line] * (long long)T + (long long)tj1 * N : nullptr;
+    double* d1 = p.w.stress ? p.w.stress + rec.stress_off : nullptr;
     double* d2 = (p.w.stress && tj2 < T) ? d1 + N : nullptr;
     double b1 = ninf, b2 = ninf;
     int i1 = 0x7fffffff, i2 = 0x7fffffff;
@@ -471,7 +479,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
       if (BLUE && q >= P1) break;
       const int m = j + q * P2;
       if (m < N) {
-        const cplx u = BLUE ? cmul(v[q], ldg_cplx(tab.post + m)) : v[q];
+        const cplx u = BLUE ? cmul(v[q], ldg_cplx(rec.post + m)) : v[q];
         const int idx = (m < halfN) ? 2 * m : 2 * (N - 1 - m) + 1;
         if (d1) __stcs(d1 + idx, u.x);
         if (d2) __stcs(d2 + idx, u.y);
@@ -506,8 +514,9 @@ __global__ void __launch_bounds__(128) em_long_reduce_kernel(const LongWave w, i
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= 2 * w.n_tr) return;
   const int s = e >> 1, which = e & 1;
-  const int line = w.tr_line[s];
-  const int tj = 2 * w.tr_pair[s] + which;
+  const SlotRec rec = w.recs[s];
+  const int line = rec.line;
+  const int tj = 2 * rec.pair + which;
   if (tj >= w.T) return;
   double b = -__longlong_as_double(0x7ff0000000000000LL);
   int bi = 0x7fffffff;
@@ -518,7 +527,7 @@ __global__ void __launch_bounds__(128) em_long_reduce_kernel(const LongWave w, i
   }
   if (bi == 0x7fffffff) {
     bi = 0;
-    b = w.stress ? w.stress[w.node_off[line] * (long long)w.T + (long long)tj * w.num_nodes[line]]
+    b = w.stress ? w.stress[rec.stress_off + (long long)which * rec.N]
                  : __longlong_as_double(0x7ff8000000000000LL);
   }
   const long long o = (long long)line * w.T + tj;

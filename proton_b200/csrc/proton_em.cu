@@ -321,7 +321,7 @@ struct proton_em_plan {
   std::vector<int> h_class_lines;    // host copy of d_class_lines
   // long-line transform lists (slot -> line, timestamp pair): they depend on (T, chunk range) only, so they are
   // built and uploaded once and reused by every later evaluation of the plan
-  struct LongList { int T, c0, c1; long long n; DevBuf<int> line, pair; };
+  struct LongList { int T, c0, c1; long long n; DevBuf<em::SlotRec> recs; };
   std::vector<LongList*> long_lists;
   std::vector<long long> node_off;   // host copy
   std::vector<int> num_nodes;        // host copy
@@ -620,7 +620,7 @@ int long_build_tables(proton_em_ctx* ctx, const em::NTab* d_e, int count, int lp
       cp.w.n_tr = cnt; cp.w.x = ctx->long_x.p;
       cp.mode = 1; cp.tabs_build = d_e + off; cp.tr_per_cta = 1; cp.twl = ctx->d_twl[lp1];
       { int rc = launch_long_colfwd(ctx, ctx->stream, lp1, cp, cnt); if (rc) return rc; }
-      em::RowParams rp{ctx->long_x.p, lp1, 1, nullptr, nullptr, nullptr, d_e + off, ctx->d_tw[em::kLongLog2P2]};
+      em::RowParams rp{ctx->long_x.p, lp1, 1, nullptr, d_e + off, ctx->d_tw[em::kLongLog2P2]};
       { int rc = launch_long_row(ctx, ctx->stream, rp, cnt); if (rc) return rc; }
     }
   }
@@ -774,7 +774,7 @@ void destroy_plan(proton_em_plan* p) {
   p->own_num_nodes.free(); p->own_a.free(); p->own_trip_off.free();
   p->d_node_off.free(); p->d_blk_off.free(); p->d_r_idx.free(); p->d_r_cnt.free(); p->d_line_tab.free();
   p->d_r_val.free(); p->d_W.free(); p->d_tabs.free(); p->d_class_lines.free(); p->d_sigma0.free();
-  for (auto* ll : p->long_lists) { ll->line.free(); ll->pair.free(); delete ll; }
+  for (auto* ll : p->long_lists) { ll->recs.free(); delete ll; }
   delete p;
 }
 
@@ -1211,26 +1211,33 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
   for (auto* c : p->long_lists)
     if (c->T == T && c->c0 == chunk_begin && c->c1 == chunk_end) { ll = c; break; }
   if (!ll) {
-    std::vector<int> tr_line((size_t)n_tr_total), tr_pair((size_t)n_tr_total);
+    // one record per transform slot (line-major, timestamp pairs of a line consecutive)
+    std::vector<em::SlotRec> recs((size_t)n_tr_total);
     size_t o = 0;
     for (const auto* cl : longs)
       for (int i = 0; i < cl->count; ++i) {
         const int line = p->h_class_lines[cl->offset + i];
-        for (int pr = 0; pr < npairs; ++pr, ++o) { tr_line[o] = line; tr_pair[o] = pr; }
+        const int N = p->num_nodes[line];
+        const em::NTab& t = ctx->tabs[N];
+        for (int pr = 0; pr < npairs; ++pr, ++o) {
+          em::SlotRec& r = recs[o];
+          r.lam = t.lam; r.W = p->d_W.p + p->node_off[line]; r.pre = t.pre; r.post = t.post; r.hhat = t.hhat;
+          r.stress_off = p->node_off[line] * (long long)T + 2LL * pr * N;
+          r.N = N; r.line = line; r.pair = pr; r.reserved = 0;
+        }
       }
     if (p->long_lists.size() >= 8) {            // a plan evaluated at many different T: drop the oldest list
       proton_em_plan::LongList* old = p->long_lists.front();
       p->long_lists.erase(p->long_lists.begin());
-      old->line.free(); old->pair.free();       // stream-ordered: earlier evaluations on ctx->stream are done with it
+      old->recs.free();                         // stream-ordered: earlier evaluations on ctx->stream are done with it
       delete old;
     }
     ll = new proton_em_plan::LongList();
     ll->T = T; ll->c0 = chunk_begin; ll->c1 = chunk_end; ll->n = n_tr_total;
     p->long_lists.push_back(ll);
-    CU_TRY(ll->line.alloc((size_t)n_tr_total));
-    CU_TRY(ll->pair.alloc((size_t)n_tr_total));
-    CU_TRY(cudaMemcpyAsync(ll->line.p, tr_line.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-    CU_TRY(cudaMemcpyAsync(ll->pair.p, tr_pair.data(), n_tr_total * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    CU_TRY(ll->recs.alloc((size_t)n_tr_total));
+    CU_TRY(cudaMemcpyAsync(ll->recs.p, recs.data(), n_tr_total * sizeof(em::SlotRec), cudaMemcpyHostToDevice, ctx->stream));
+    CU_TRY(cudaStreamSynchronize(ctx->stream));   // `recs` is pageable host memory that goes away at the end of this block
   }
   *list_out = ll;
   // fork: the lanes start after everything queued so far on the main stream (uploads above included)
@@ -1252,9 +1259,8 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
       cudaStream_t st = ctx->lane[li];
       em::cplx* xbuf = ctx->long_x.p + (size_t)li * lane_stride;
       em::LongWave w{};
-      w.tr_line = ll->line.p + base + s0; w.tr_pair = ll->pair.p + base + s0; w.n_tr = cnt; w.T = T;
-      w.num_nodes = p->d_num_nodes; w.a_coeff = p->d_a; w.node_off = p->d_node_off.p; w.line_tab = p->d_line_tab.p;
-      w.tabs = p->d_tabs.p; w.W = p->d_W.p; w.ts = d_ts; w.exp_tab = ctx->d_exp;
+      w.recs = ll->recs.p + base + s0; w.n_tr = cnt; w.T = T;
+      w.a_coeff = p->d_a; w.ts = d_ts;
       w.x = xbuf; w.stress = d_stress; w.tr_base = (int)(base + s0);
       w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p;
       w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
@@ -1263,7 +1269,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
       const int tpc = std::max(1, cnt / col_div);
       const int groups = (cnt + tpc - 1) / tpc;
       em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
-      em::RowParams rp{xbuf, lp1, blue ? 0 : 2, w.tr_line, p->d_line_tab.p, p->d_tabs.p, nullptr,
+      em::RowParams rp{xbuf, lp1, blue ? 0 : 2, w.recs, nullptr,
                        ctx->d_tw[em::kLongLog2P2]};
       int rc;
       if (blue) rc = launch_long_colfwd_paired(ctx, st, lp1, cp, groups);
@@ -1291,8 +1297,8 @@ static int eval_long_finish(proton_em_plan* p, const proton_em_plan::LongList* l
   }
   if (n_tr_total <= 0) return PROTON_EM_OK;
   em::LongWave w{};
-  w.tr_line = ll->line.p; w.tr_pair = ll->pair.p; w.n_tr = (int)n_tr_total; w.T = T;
-  w.num_nodes = p->d_num_nodes; w.node_off = p->d_node_off.p; w.stress = d_stress;
+  w.recs = ll->recs.p; w.n_tr = (int)n_tr_total; w.T = T;
+  w.stress = d_stress;
   w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p; w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
   w.critical = critical;
   {
