@@ -124,6 +124,7 @@ struct alignas(16) SlotRec {
   const cplx* post;        // post-chirp (Bluestein)
   const cplx* hhat;        // transformed chirp (Bluestein)
   long long stress_off;    // node_off[line] * T + 2 * pair * N: first timestamp's row in the stress field
+  double a;                // A_coeff of the line
   int N;
   int line;
   int pair;
@@ -136,7 +137,6 @@ struct LongWave {
   int n_tr;
   int tr_base;           // index of slot 0 among all transforms of the class (partials are per class)
   int T;
-  const double* a_coeff;
   const double* ts;
   cplx* x;               // [n_tr][P]
   double* stress;
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
       }
     }
     const double* W = rec.W;
-    const double av = p.w.a_coeff[line];
+    const double av = rec.a;
     const double t1 = p.w.ts[2 * pr];
     const double t2 = (2 * pr + 1 < p.w.T) ? p.w.ts[2 * pr + 1] : t1;
     const double w1 = __dmul_rn(av, t1), w2 = __dmul_rn(av, t2);
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(256) em_long_scatter_kernel(const LongWave w) 
   const int line = rec.line;
   const int N = rec.N;
   const double* W = rec.W;
-  const double a = w.a_coeff[line];
+  const double a = rec.a;
   const int pr = rec.pair;
   const double t1 = w.ts[2 * pr];
   const double t2 = (2 * pr + 1 < w.T) ? w.ts[2 * pr + 1] : t1;

@@ -325,6 +325,7 @@ struct proton_em_plan {
   std::vector<LongList*> long_lists;
   std::vector<long long> node_off;   // host copy
   std::vector<int> num_nodes;        // host copy
+  std::vector<double> a_host;        // host copy of a_coeff
 };
 
 namespace {
@@ -996,11 +997,14 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
   // ---- host view of the per-line sizes -----------------------------------------------------
   p->num_nodes.resize(L);
   std::vector<long long> trip_off(L + 1), u_off(L + 1);
+  p->a_host.resize(L);
   if (location == PROTON_EM_HOST) {
+    std::memcpy(p->a_host.data(), b->a_coeff, L * sizeof(double));
     std::memcpy(p->num_nodes.data(), b->num_nodes, L * sizeof(int));
     for (int64_t i = 0; i <= L; ++i) { trip_off[i] = b->trip_off[i]; u_off[i] = b->u_off[i]; }
   } else {
     CU_TRY(cudaMemcpy(p->num_nodes.data(), b->num_nodes, L * sizeof(int), cudaMemcpyDeviceToHost));
+    CU_TRY(cudaMemcpy(p->a_host.data(), b->a_coeff, L * sizeof(double), cudaMemcpyDeviceToHost));
     CU_TRY(cudaMemcpy(trip_off.data(), b->trip_off, (L + 1) * sizeof(long long), cudaMemcpyDeviceToHost));
     CU_TRY(cudaMemcpy(u_off.data(), b->u_off, (L + 1) * sizeof(long long), cudaMemcpyDeviceToHost));
   }
@@ -1223,6 +1227,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
           em::SlotRec& r = recs[o];
           r.lam = t.lam; r.W = p->d_W.p + p->node_off[line]; r.pre = t.pre; r.post = t.post; r.hhat = t.hhat;
           r.stress_off = p->node_off[line] * (long long)T + 2LL * pr * N;
+          r.a = p->a_host[line];
           r.N = N; r.line = line; r.pair = pr; r.reserved = 0;
         }
       }
@@ -1260,7 +1265,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
       em::cplx* xbuf = ctx->long_x.p + (size_t)li * lane_stride;
       em::LongWave w{};
       w.recs = ll->recs.p + base + s0; w.n_tr = cnt; w.T = T;
-      w.a_coeff = p->d_a; w.ts = d_ts;
+      w.ts = d_ts;
       w.x = xbuf; w.stress = d_stress; w.tr_base = (int)(base + s0);
       w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p;
       w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
