@@ -271,14 +271,19 @@ __global__ void __launch_bounds__(128) em_long_colfwd_paired_kernel(const ColPar
     const double t2 = (2 * pr + 1 < p.w.T) ? p.w.ts[2 * pr + 1] : t1;
     const double w1 = __dmul_rn(av, t1), w2 = __dmul_rn(av, t2);
     cplx yk[QMAX];
+    double lq[QMAX], wq[QMAX];
+#pragma unroll
+    for (int q = 0; q < QMAX; ++q) {              // all loads first, then the arithmetic: written as one loop, the
+                                                  // compiler issued each mode's loads right before its exp (-3 % per step)
+      const int k = j + q * P2;
+      lq[q] = 0.0; wq[q] = 0.0;
+      if (active && q < P1 && k < N) { lq[q] = __ldg(rec.lam + k); wq[q] = __ldg(W + k); }
+    }
 #pragma unroll
     for (int q = 0; q < QMAX; ++q) {
       const int k = j + q * P2;
       yk[q] = cplx{0.0, 0.0};
-      if (active && q < P1 && k < N) {
-        const double l = rec.lam[k], wk = W[k];
-        yk[q] = cplx{em_modal(l, wk, w1, t1), em_modal(l, wk, w2, t2)};
-      }
+      if (active && q < P1 && k < N) yk[q] = cplx{em_modal(lq[q], wq[q], w1, t1), em_modal(lq[q], wq[q], w2, t2)};
       ys[q * 128 + tid] = yk[q];
     }
     __syncthreads();
