@@ -127,13 +127,27 @@ __global__ void __launch_bounds__(MixCfg<LR, ODD>::NT, MixCfg<LR, ODD>::MINB) em
     // ---- modal values -> chirped packed spectrum at its natural position (row k / R, column k % R) ----------------
     {
       const int KP = (N - 1) >> 1;
-      for (int k = tid + 1; k <= KP; k += NT) {
-        const int kk = N - k;
-        const double lamk = lam[k], wk = W[k], lamkk = lam[kk], wkk = W[kk];
-        const double y1k = em_modal(lamk, wk, w1, t1), y2k = em_modal(lamk, wk, w2, t2);
-        const double y1kk = em_modal(lamkk, wkk, w1, t1), y2kk = em_modal(lamkk, wkk, w2, t2);
-        data[(k >> LR) * RS + pad_idx<LR>(k & (R - 1))] = cmul(ldg_cplx(tab.pre + k), cplx{y1k + y2kk, y2k - y1kk});
-        data[(kk >> LR) * RS + pad_idx<LR>(kk & (R - 1))] = cmul(ldg_cplx(tab.pre + kk), cplx{y1kk + y2k, y2kk - y1k});
+      // software pipeline: the loads of the next mode pair are issued before the four exponentials of this one
+      // (the tables of a line exceed what is left of L1 beside the rows, so each pass over them pays L2 latency: +3 %)
+      int k = tid + 1;
+      double lamk = 0.0, wk = 0.0, lamkk = 0.0, wkk = 0.0;
+      cplx prek = cplx{0.0, 0.0}, prekk = cplx{0.0, 0.0};
+      if (k <= KP) {
+        lamk = __ldg(lam + k); wk = __ldg(W + k); lamkk = __ldg(lam + N - k); wkk = __ldg(W + N - k);
+        prek = ldg_cplx(tab.pre + k); prekk = ldg_cplx(tab.pre + N - k);
+      }
+      for (; k <= KP; k += NT) {
+        const int kk = N - k, kn = k + NT;
+        const double l0 = lamk, w0 = wk, l1 = lamkk, ww1 = wkk;
+        const cplx p0 = prek, pp1 = prekk;
+        if (kn <= KP) {
+          lamk = __ldg(lam + kn); wk = __ldg(W + kn); lamkk = __ldg(lam + N - kn); wkk = __ldg(W + N - kn);
+          prek = ldg_cplx(tab.pre + kn); prekk = ldg_cplx(tab.pre + N - kn);
+        }
+        const double y1k = em_modal(l0, w0, w1, t1), y2k = em_modal(l0, w0, w2, t2);
+        const double y1kk = em_modal(l1, ww1, w1, t1), y2kk = em_modal(l1, ww1, w2, t2);
+        data[(k >> LR) * RS + pad_idx<LR>(k & (R - 1))] = cmul(p0, cplx{y1k + y2kk, y2k - y1kk});
+        data[(kk >> LR) * RS + pad_idx<LR>(kk & (R - 1))] = cmul(pp1, cplx{y1kk + y2k, y2kk - y1k});
       }
       if (tid < 2) {
         const int k = tid ? (N >> 1) : 0;
