@@ -468,6 +468,16 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
     const int N = rec.N;
     const int halfN = (N + 1) >> 1;
     const cplx* x = p.w.x + (long long)s * P;
+    // the post-chirp values of this thread's outputs: asked for first, needed last
+    constexpr int QNE = BLUE ? ((P1 + 1) / 2 + 1 < P1 ? (P1 + 1) / 2 + 1 : P1) : 1;
+    cplx postq[QNE];
+    if (BLUE) {
+#pragma unroll
+      for (int q = 0; q < QNE; ++q) {
+        postq[q] = cplx{1.0, 0.0};
+        if (j + q * P2 < N) postq[q] = ldg_cplx(rec.post + j + q * P2);
+      }
+    }
     cplx v[P1];
 #pragma unroll
     for (int r = 0; r < P1; ++r) v[r] = x[(long long)r * P2 + j];
@@ -484,7 +494,7 @@ __global__ void __launch_bounds__(kLongColsPerCta) em_long_colinv_kernel(const C
       if (BLUE && q >= P1) break;
       const int m = j + q * P2;
       if (m < N) {
-        const cplx u = BLUE ? cmul(v[q], ldg_cplx(rec.post + m)) : v[q];
+        const cplx u = BLUE ? cmul(v[q], postq[q < QNE ? q : 0]) : v[q];
         const int idx = (m < halfN) ? 2 * m : 2 * (N - 1 - m) + 1;
         if (d1) __stcs(d1 + idx, u.x);
         if (d2) __stcs(d2 + idx, u.y);
