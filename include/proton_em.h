@@ -152,6 +152,15 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* batch, con
  * `msg` receives the text the reference prints to stdout before exit(1). */
 int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_t msg_len);
 
+/* Level 1, batched: n analytical.cfg files in one call — what PROTON_cli.analyze starts as one process per line
+ * (PROTON_cli.py:1174-1181).  Every cfg is read like proton_em_run_cfg reads it; the lines that read cleanly form ONE
+ * batch, evaluated once at the distinct simulation times they name; every line's stress_<t>.txt is written where the
+ * reference process would write it.  status[i] (may be NULL) receives the code of cfg i.  Returns the number of cfgs
+ * that failed (0 = all written), or a negative PROTON_EM_E* code if the batched evaluation itself failed; `msg` holds
+ * the reference's stdout text of the first failure. */
+int proton_em_run_cfgs(proton_em_ctx* ctx, const char* const* cfg_paths, int64_t n, int32_t* status, char* msg,
+                       size_t msg_len);
+
 /* One line with no allocation anywhere (this entry point has no counterpart in the reference, which
  * allocates freely inside its own process).  It exists for callers that must not ask the CUDA runtime for
  * memory: hosts that gave all device memory to their own pool, plug-ins called where cudaMalloc would stall

@@ -48,7 +48,7 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_plan_scratch_bytes", "proton_em_eval", "proton_em_synchronize", "proton_em_stream",
            "proton_em_launch_count", "proton_em_analyze_host", "proton_em_run_cfg", "proton_em_debug_exp",
            "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read",
-           "proton_em_analyze_history_host", "proton_em_debug_line_table", "proton_em_pack_sigma0"]
+           "proton_em_analyze_history_host", "proton_em_debug_line_table", "proton_em_pack_sigma0", "proton_em_run_cfgs"]
 
 
 def load() -> ctypes.CDLL:
@@ -80,6 +80,9 @@ def load() -> ctypes.CDLL:
     lib.proton_em_analyze_host.argtypes = [vp, ctypes.POINTER(Batch), vp, ctypes.c_int32, ctypes.POINTER(Opts),
                                            ctypes.POINTER(Result), ctypes.c_int64]
     lib.proton_em_run_cfg.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t]
+    if hasattr(lib, "proton_em_run_cfgs"):
+        lib.proton_em_run_cfgs.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p), ctypes.c_int64, c_i32p, ctypes.c_char_p,
+                                           ctypes.c_size_t]
     lib.proton_em_debug_exp.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_debug_expm1.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_eval_line_noalloc.argtypes = [ctypes.c_int, vp, ctypes.c_int32, ctypes.c_double, ctypes.c_int32, vp, vp,

@@ -256,6 +256,18 @@ class Context:
         return rc, buf.value.decode(errors="replace")
 
 
+    def run_cfgs(self, cfg_paths):
+        """Many analytical.cfg files as one batch (proton_em_run_cfgs) -> (failed count or negative code, per-cfg status
+        array, stdout text of the first failure)."""
+        paths = [str(p).encode() for p in cfg_paths]
+        arr = (ctypes.c_char_p * len(paths))(*paths)
+        status = np.zeros(len(paths), dtype=np.int32)
+        buf = ctypes.create_string_buffer(2048)
+        rc = self._lib.proton_em_run_cfgs(self._h, arr, len(paths), status.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
+                                          buf, len(buf))
+        return rc, status, buf.value.decode(errors="replace")
+
+
 class Plan:
     def __init__(self, ctx: Context, handle, node_off: np.ndarray, keep):
         self.ctx = ctx

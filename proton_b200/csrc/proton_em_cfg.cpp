@@ -1,4 +1,5 @@
-// proton_em_cfg.cpp — Level-1 entry point: what the reference PROCESS does for one analytical.cfg.
+// proton_em_cfg.cpp — Level-1 entry points: what the reference PROCESS does for one analytical.cfg (proton_em_run_cfg),
+// and the same for many cfgs in one batched evaluation (proton_em_run_cfgs).
 //
 // Mirrors main / simulation_engine::read_file / analyical_wrapper / tripletParser of the reference
 // binary (bin/EMtool_analytical@0x6920, @0xaaf4, @0xb93c, @0xb010), including
@@ -55,11 +56,19 @@ std::vector<std::string> tokenize(const std::string& line) {   // boost::char_se
   return out;
 }
 
-}  // namespace
+// What one analytical.cfg names: the line's inputs as the reference process reads them.
+struct CfgLine {
+  std::string out_dir;
+  int32_t N = 0;
+  double a_coeff = 0.0, sim_time = 0.0;
+  std::vector<double> u;
+  std::vector<int32_t> rows, cols;
+  std::vector<double> vals;
+};
 
-extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_t msg_len) {
-  set_msg(msg, msg_len, "");
-  if (!cfg_path) { set_msg(msg, msg_len, "Wrong number of arguments. Configuration file expected.\n"); return PROTON_EM_EINVAL; }
+// read_file + the reading half of analyical_wrapper; on failure `text` is what the reference prints before exit(1).
+int read_cfg_line(const char* cfg_path, CfgLine& out, std::string& text) {
+  if (!cfg_path) { text = "Wrong number of arguments. Configuration file expected.\n"; return PROTON_EM_EINVAL; }
   // ---- read_file: "key value" per line, later keys override, unknown keys ignored -----------------
   std::string input_files;
   long num_nodes = 0;
@@ -78,23 +87,22 @@ extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char*
       else if (key == "simulation_time") { double v; if (is >> v) { sim_time = v; have_t = true; } }
     }
   }
-  if (!have_in) { set_msg(msg, msg_len, std::string(cfg_path) + " The configuration file does not include the input directory.\n"); return PROTON_EM_EINVAL; }
-  if (!have_n) { set_msg(msg, msg_len, "The configuration file does not include the number of nodes.\n"); return PROTON_EM_EINVAL; }
-  if (!have_a) { set_msg(msg, msg_len, "The configuration file does not include the A coefficient.\n"); return PROTON_EM_EINVAL; }
-  if (!have_t) { set_msg(msg, msg_len, "The configuration file does not include the target simulation time.\n"); return PROTON_EM_EINVAL; }
-  if (num_nodes <= 0 || num_nodes > 0x7fffffffL) { set_msg(msg, msg_len, "num_nodes must be a positive 32-bit integer.\n"); return PROTON_EM_EINVAL; }
+  if (!have_in) { text = std::string(cfg_path) + " The configuration file does not include the input directory.\n"; return PROTON_EM_EINVAL; }
+  if (!have_n) { text = "The configuration file does not include the number of nodes.\n"; return PROTON_EM_EINVAL; }
+  if (!have_a) { text = "The configuration file does not include the A coefficient.\n"; return PROTON_EM_EINVAL; }
+  if (!have_t) { text = "The configuration file does not include the target simulation time.\n"; return PROTON_EM_EINVAL; }
+  if (num_nodes <= 0 || num_nodes > 0x7fffffffL) { text = "num_nodes must be a positive 32-bit integer.\n"; return PROTON_EM_EINVAL; }
 
   // ---- analyical_wrapper: output directory, curden.csv, B.csv ------------------------------------
   const size_t pos = input_files.find("input");
-  if (pos == std::string::npos) { set_msg(msg, msg_len, "The input directory path does not contain \"input\".\n"); return PROTON_EM_EINVAL; }
-  std::string out_dir = input_files;
-  out_dir.replace(pos, 5, "output");
-
-  std::vector<double> u;
+  if (pos == std::string::npos) { text = "The input directory path does not contain \"input\".\n"; return PROTON_EM_EINVAL; }
+  out.out_dir = input_files;
+  out.out_dir.replace(pos, 5, "output");
+  out.N = (int32_t)num_nodes; out.a_coeff = a_coeff; out.sim_time = sim_time;
   {
     const std::string path = input_files + "curden.csv";
     std::ifstream f(path);
-    if (!f) { set_msg(msg, msg_len, "The file " + path + " was not found.\nTerminating.\n"); return PROTON_EM_EIO; }
+    if (!f) { text = "The file " + path + " was not found.\nTerminating.\n"; return PROTON_EM_EIO; }
     std::string line;
     size_t lineno = 0;
     while (std::getline(f, line)) {
@@ -103,66 +111,147 @@ extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char*
       errno = 0;
       const double v = std::strtod(line.c_str(), &end);
       if (end == line.c_str()) {
-        set_msg(msg, msg_len, "Error parsing file " + path + " at line " + std::to_string(lineno) + ".\nTerminating.\n");
+        text = "Error parsing file " + path + " at line " + std::to_string(lineno) + ".\nTerminating.\n";
         return PROTON_EM_EINVAL;
       }
-      u.push_back(v);
+      out.u.push_back(v);
     }
   }
-  std::vector<int32_t> rows, cols;
-  std::vector<double> vals;
   {
     const std::string path = input_files + "B.csv";
     std::ifstream f(path);
-    if (!f) { set_msg(msg, msg_len, "Terminating\nThe file " + path + " was not found.\nTerminating.\n"); return PROTON_EM_EIO; }
+    if (!f) { text = "Terminating\nThe file " + path + " was not found.\nTerminating.\n"; return PROTON_EM_EIO; }
     std::string line;
     size_t lineno = 0;
     while (std::getline(f, line)) {
       ++lineno;
       const std::vector<std::string> tok = tokenize(line);
       if (tok.empty()) continue;
-      if (tok.size() < 2) { set_msg(msg, msg_len, "Required second value at line " + std::to_string(lineno) + " of the file " + path + ".\nTerminating.\n"); return PROTON_EM_EINVAL; }
-      if (tok.size() < 3) { set_msg(msg, msg_len, "Required third value at line " + std::to_string(lineno) + " of the file " + path + ".\nTerminating.\n"); return PROTON_EM_EINVAL; }
+      if (tok.size() < 2) { text = "Required second value at line " + std::to_string(lineno) + " of the file " + path + ".\nTerminating.\n"; return PROTON_EM_EINVAL; }
+      if (tok.size() < 3) { text = "Required third value at line " + std::to_string(lineno) + " of the file " + path + ".\nTerminating.\n"; return PROTON_EM_EINVAL; }
       char* e1 = nullptr; char* e2 = nullptr;
       const long r = std::strtol(tok[0].c_str(), &e1, 10), c = std::strtol(tok[1].c_str(), &e2, 10);
       if (e1 == tok[0].c_str() || e2 == tok[1].c_str()) {
-        set_msg(msg, msg_len, "Error parsing file " + path + " at line " + std::to_string(lineno) + ".\nTerminating.\n");
+        text = "Error parsing file " + path + " at line " + std::to_string(lineno) + ".\nTerminating.\n";
         return PROTON_EM_EINVAL;
       }
-      rows.push_back((int32_t)r); cols.push_back((int32_t)c); vals.push_back(std::atof(tok[2].c_str()));
+      out.rows.push_back((int32_t)r); out.cols.push_back((int32_t)c); out.vals.push_back(std::atof(tok[2].c_str()));
     }
   }
-  for (size_t i = 0; i < rows.size(); ++i) {
-    if (rows[i] < 0 || rows[i] >= num_nodes || cols[i] < 0 || (size_t)cols[i] >= u.size()) {
-      set_msg(msg, msg_len, "B.csv entry " + std::to_string(i + 1) + " lies outside the " + std::to_string(num_nodes) + " x " +
-                                std::to_string(u.size()) + " matrix.\nTerminating.\n");
+  for (size_t i = 0; i < out.rows.size(); ++i) {
+    if (out.rows[i] < 0 || out.rows[i] >= num_nodes || out.cols[i] < 0 || (size_t)out.cols[i] >= out.u.size()) {
+      text = "B.csv entry " + std::to_string(i + 1) + " lies outside the " + std::to_string(num_nodes) + " x " +
+             std::to_string(out.u.size()) + " matrix.\nTerminating.\n";
       return PROTON_EM_EINVAL;
     }
   }
+  return PROTON_EM_OK;
+}
 
-  // ---- analytical(): one line, one timestamp on the GPU -----------------------------------------
-  if (!ctx) { set_msg(msg, msg_len, "No CUDA context.\n"); return PROTON_EM_ECUDA; }
-  const int32_t N = (int32_t)num_nodes;
-  const int64_t trip_off[2] = {0, (int64_t)rows.size()};
-  const int64_t u_off[2] = {0, (int64_t)u.size()};
-  proton_em_batch batch{1, &N, &a_coeff, trip_off, rows.data(), cols.data(), vals.data(), u_off, u.data()};
-  std::vector<double> stress((size_t)N);
-  double mx = 0.0; int32_t amx = 0; uint8_t flag = 0;
-  proton_em_result res{stress.data(), &mx, &amx, &flag};
-  proton_em_opts opts{0.0, PROTON_EM_ALG_AUTO, 0};
-  const int rc = proton_em_analyze_host(ctx, &batch, &sim_time, 1, &opts, &res, 0);
-  if (rc != PROTON_EM_OK) { set_msg(msg, msg_len, std::string(proton_em_last_error()) + "\nTerminating.\n"); return rc; }
-
-  // ---- stress_<%f>.txt, one "%.18g" per line ----------------------------------------------------
-  const std::string fname = out_dir + "stress_" + std::to_string(sim_time) + ".txt";
+// stress_<%f>.txt, one "%.18g" per line (the writing half of analyical_wrapper)
+int write_stress_file(const CfgLine& ln, const double* stress, std::string& text) {
+  const std::string fname = ln.out_dir + "stress_" + std::to_string(ln.sim_time) + ".txt";
   const size_t slash = fname.find_last_of('/');
   if (slash != std::string::npos && !make_dirs(fname.substr(0, slash))) {
-    set_msg(msg, msg_len, "Cannot create the output directory " + fname.substr(0, slash) + ".\nTerminating.\n");
+    text = "Cannot create the output directory " + fname.substr(0, slash) + ".\nTerminating.\n";
     return PROTON_EM_EIO;
   }
   FILE* fo = std::fopen(fname.c_str(), "w");
-  if (!fo) { set_msg(msg, msg_len, "Cannot open " + fname + " for writing.\nTerminating.\n"); return PROTON_EM_EIO; }
-  for (int32_t i = 0; i < N; ++i) std::fprintf(fo, "%.18g\n", stress[(size_t)i]);
+  if (!fo) { text = "Cannot open " + fname + " for writing.\nTerminating.\n"; return PROTON_EM_EIO; }
+  for (int32_t i = 0; i < ln.N; ++i) std::fprintf(fo, "%.18g\n", stress[(size_t)i]);
   std::fclose(fo);
   return PROTON_EM_OK;
+}
+
+}  // namespace
+
+extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_t msg_len) {
+  set_msg(msg, msg_len, "");
+  CfgLine ln;
+  std::string text;
+  { const int rc = read_cfg_line(cfg_path, ln, text); if (rc) { set_msg(msg, msg_len, text); return rc; } }
+  // ---- analytical(): one line, one timestamp on the GPU -----------------------------------------
+  if (!ctx) { set_msg(msg, msg_len, "No CUDA context.\n"); return PROTON_EM_ECUDA; }
+  const int64_t trip_off[2] = {0, (int64_t)ln.rows.size()};
+  const int64_t u_off[2] = {0, (int64_t)ln.u.size()};
+  proton_em_batch batch{1, &ln.N, &ln.a_coeff, trip_off, ln.rows.data(), ln.cols.data(), ln.vals.data(), u_off, ln.u.data()};
+  std::vector<double> stress((size_t)ln.N);
+  double mx = 0.0; int32_t amx = 0; uint8_t flag = 0;
+  proton_em_result res{stress.data(), &mx, &amx, &flag};
+  proton_em_opts opts{0.0, PROTON_EM_ALG_AUTO, 0};
+  const int rc = proton_em_analyze_host(ctx, &batch, &ln.sim_time, 1, &opts, &res, 0);
+  if (rc != PROTON_EM_OK) { set_msg(msg, msg_len, std::string(proton_em_last_error()) + "\nTerminating.\n"); return rc; }
+  const int wrc = write_stress_file(ln, stress.data(), text);
+  if (wrc) set_msg(msg, msg_len, text);
+  return wrc;
+}
+
+// Many analytical.cfg files in one call — what PROTON_cli.analyze starts as one process per line
+// (PROTON_cli.py:1174-1181).  Every cfg is read like proton_em_run_cfg reads it; the lines that read cleanly form ONE
+// batch, evaluated once at the distinct simulation times they ask for, and every line's stress_<t>.txt is written where
+// the reference process would write it.  status[i] receives the code of cfg i (0 ok); the return value is the number of
+// cfgs that failed, or a negative PROTON_EM_E* code if the batched evaluation itself failed (message in `msg`, which
+// otherwise holds the reference's stdout text of the first failing cfg).
+extern "C" int proton_em_run_cfgs(proton_em_ctx* ctx, const char* const* cfg_paths, int64_t n, int32_t* status,
+                                  char* msg, size_t msg_len) {
+  set_msg(msg, msg_len, "");
+  if (n < 0 || (n > 0 && !cfg_paths)) { set_msg(msg, msg_len, "proton_em_run_cfgs: bad arguments.\n"); return PROTON_EM_EINVAL; }
+  if (!ctx) { set_msg(msg, msg_len, "No CUDA context.\n"); return PROTON_EM_ECUDA; }
+  std::vector<CfgLine> lines((size_t)n);
+  std::vector<int64_t> good;
+  int failed = 0;
+  bool have_msg = false;
+  for (int64_t i = 0; i < n; ++i) {
+    std::string text;
+    const int rc = read_cfg_line(cfg_paths[i], lines[(size_t)i], text);
+    if (status) status[i] = rc;
+    if (rc) { ++failed; if (!have_msg) { set_msg(msg, msg_len, text); have_msg = true; } }
+    else good.push_back(i);
+  }
+  if (good.empty()) return failed;
+  // one batch over the good lines, evaluated at the distinct times
+  std::vector<double> ts;
+  std::vector<int> t_of(good.size());
+  for (size_t g = 0; g < good.size(); ++g) {
+    const double t = lines[(size_t)good[g]].sim_time;
+    size_t k = 0;
+    while (k < ts.size() && ts[k] != t) ++k;
+    if (k == ts.size()) ts.push_back(t);
+    t_of[g] = (int)k;
+  }
+  const int64_t L = (int64_t)good.size();
+  const int32_t T = (int32_t)ts.size();
+  std::vector<int32_t> nn((size_t)L), rows, cols;
+  std::vector<double> aa((size_t)L), vals, u;
+  std::vector<int64_t> trip_off((size_t)L + 1, 0), u_off((size_t)L + 1, 0), node_off((size_t)L + 1, 0);
+  for (int64_t g = 0; g < L; ++g) {
+    const CfgLine& ln = lines[(size_t)good[(size_t)g]];
+    nn[(size_t)g] = ln.N; aa[(size_t)g] = ln.a_coeff;
+    rows.insert(rows.end(), ln.rows.begin(), ln.rows.end());
+    cols.insert(cols.end(), ln.cols.begin(), ln.cols.end());
+    vals.insert(vals.end(), ln.vals.begin(), ln.vals.end());
+    u.insert(u.end(), ln.u.begin(), ln.u.end());
+    trip_off[(size_t)g + 1] = (int64_t)rows.size(); u_off[(size_t)g + 1] = (int64_t)u.size();
+    node_off[(size_t)g + 1] = node_off[(size_t)g] + ln.N;
+  }
+  proton_em_batch batch{L, nn.data(), aa.data(), trip_off.data(), rows.data(), cols.data(), vals.data(), u_off.data(), u.data()};
+  std::vector<double> stress((size_t)node_off[(size_t)L] * (size_t)T), mx((size_t)L * T);
+  std::vector<int32_t> amx((size_t)L * T);
+  std::vector<uint8_t> flag((size_t)L * T);
+  proton_em_result res{stress.data(), mx.data(), amx.data(), flag.data()};
+  proton_em_opts opts{0.0, PROTON_EM_ALG_AUTO, 0};
+  const int rc = proton_em_analyze_host(ctx, &batch, ts.data(), T, &opts, &res, 0);
+  if (rc != PROTON_EM_OK) { set_msg(msg, msg_len, std::string(proton_em_last_error()) + "\nTerminating.\n"); return rc; }
+  for (int64_t g = 0; g < L; ++g) {
+    const CfgLine& ln = lines[(size_t)good[(size_t)g]];
+    std::string text;
+    const double* row = stress.data() + (size_t)node_off[(size_t)g] * (size_t)T + (size_t)t_of[(size_t)g] * (size_t)ln.N;
+    const int wrc = write_stress_file(ln, row, text);
+    if (wrc) {
+      if (status) status[good[(size_t)g]] = wrc;
+      ++failed;
+      if (!have_msg) { set_msg(msg, msg_len, text); have_msg = true; }
+    }
+  }
+  return failed;
 }

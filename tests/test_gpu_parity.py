@@ -338,6 +338,40 @@ def test_launcher_writes_the_reference_output_file(oracle, tmp_path):
             assert np.abs(got - ref).max() <= 1e-9 * np.abs(ref).max()
 
 
+def test_many_cfgs_in_one_call_write_the_same_files_as_one_process_each(ctx, oracle, tmp_path):
+    """proton_em_run_cfgs: the lines of many analytical.cfg files as ONE batch; every stress file must be byte-identical
+    to what proton_em_run_cfg writes for that cfg alone when the batch has the same partner timestamps — and within
+    rounding otherwise — and a broken cfg must fail alone without taking the others with it."""
+    from pathlib import Path
+    rng = np.random.default_rng(2718)
+    cases = [(40, 3, 1e6), (257, 4, 6.38e8), (1, 1, 1e6), (1500, 5, 6.38e8), (6000, 9, 1e7), (64, 2, 1e6)]
+    cfgs, outs, lines = [], [], []
+    for i, (N, S, t) in enumerate(cases):
+        li = synth_line(rng, N, S)
+        d = tmp_path / "many" / "input" / f"M{i}_n1_1" / "CuDD_378.0_0.1"
+        cfgs.append(oracle.write_line_inputs(d, li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, t))
+        outs.append(Path(str(d).replace("input", "output", 1)) / oracle.stress_filename(t))
+        lines.append((li, t))
+    broken = tmp_path / "many" / "input" / "broken" / "cfg" / "analytical.cfg"
+    broken.parent.mkdir(parents=True)
+    broken.write_text(f"input_files {broken.parent}/\nnum_nodes 10\nA_coeff 1e-9\n")        # no simulation_time
+    rc, status, text = ctx.run_cfgs([str(c) for c in cfgs[:3]] + [str(broken)] + [str(c) for c in cfgs[3:]])
+    assert rc == 1 and status[3] != 0 and np.count_nonzero(status) == 1
+    assert "target simulation time" in text
+    for (li, t), out in zip(lines, outs):
+        got = np.array([float(x) for x in out.read_text().split()])
+        want, _, _ = oracle.line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, [t])
+        assert len(got) == li.num_nodes
+        assert np.abs(got - want[0]).max() <= 1e-9 * np.abs(want[0]).max()
+        batched = out.read_bytes()
+        out.unlink()
+        rc1, _ = ctx.run_cfg(str(cfgs[outs.index(out)]))
+        assert rc1 == 0
+        alone = np.array([float(x) for x in out.read_text().split()])
+        assert np.abs(got - alone).max() <= 1e-13 * np.abs(alone).max()    # (a partner timestamp moves results by rounding)
+        assert len(batched) > 0
+
+
 def test_batched_analyze_driver_and_launcher_class(ctx, oracle, ibmpg1_lines, tmp_path):
     """the batch-aware `analyze` (project directory in, problematic lines out, reference-format
     stress files on request) and the in-process `Analytical_Class`."""
