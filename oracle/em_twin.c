@@ -10,6 +10,7 @@
  *   em_twin_blue    em_eval_fft_kernel<p,true>   proton_b200/csrc/em_fft.cuh       (other N <= 4096: Bluestein, P = 2^p)
  *   em_twin_rows    em_eval_mix_kernel<LR,ROWS>  proton_b200/csrc/em_mix.cuh       (Bluestein, P = 5 or 6 rows of 2^LR)
  *                   em_long_colfwd_paired / em_long_row / em_long_colinv            (4096 < N <= 65536: P = P1 x 4096)
+ *   em_twin_long_pow2  em_long_scatter / em_long_row (inverse only) / em_long_colinv (N = 2^p, 16384..131072)
  * Inputs that come from the DEVICE's sincospi (pre-twiddles, cosine table, modal weights W) are read back through
  * proton_em_debug_line_table and handed in (also the transformed chirp H, which the device builds with the same
  * kernels); lambda is the host-libm table both sides share; the stage twiddles and the small-DFT twiddles are
@@ -578,6 +579,49 @@ int em_twin_rows(int N, double a, const double* lam, const double* W, const doub
       }
     }
   }
+  free(data);
+  free(tw);
+  return 0;
+}
+
+
+/* ---- power-of-two long lines: em_long_scatter_kernel -> em_long_row_kernel (mode 2) -> em_long_colinv_kernel<P1, false>.
+ * N = P1 x 4096; U_k goes to row k mod P1, digit-reversed place of k / P1 inside the row; rows are DIT-transformed,
+ * then the column pass.  twl[j] = w_N^{+j}, j < 4096, read back from the device. */
+int em_twin_long_pow2(int N, double a, const double* lam, const double* W, const double* pre_ri, const double* twl_ri,
+                      int T, const double* ts, double* stress) {
+  const int R = 4096, lr = 12, P1 = N / R;
+  if (P1 * R != N || (P1 & (P1 - 1)) != 0 || P1 < 2 || P1 > 32) return -1;
+  int log2p1 = 0;
+  while ((1 << log2p1) < P1) ++log2p1;
+  const cplx *pre = (const cplx*)pre_ri, *twl = (const cplx*)twl_ri;
+  cplx* tw = build_stage_tw(lr);
+  cplx* nat = (cplx*)calloc((size_t)N, sizeof(cplx));
+  cplx* data = (cplx*)calloc((size_t)N, sizeof(cplx));
+  const int NST = plan_n(lr), halfN = (N + 1) >> 1;
+  for (int pr = 0; pr < (T + 1) / 2; ++pr) {
+    const int j1 = 2 * pr;
+    const double t1 = ts[j1], t2 = (j1 + 1 < T) ? ts[j1 + 1] : t1;
+    blue_modal(nat, N, a, lam, W, pre, t1, t2, 0);
+    for (int k = 0; k < N; ++k) data[(size_t)(k & (P1 - 1)) * R + digit_pos(lr, k >> log2p1)] = nat[k];
+    for (int r = 0; r < P1; ++r)
+      for (int i = NST - 1; i >= 0; --i) dit_stage(data + (size_t)r * R, lr, i, tw);
+    double* s1 = stress + (size_t)j1 * N;
+    double* s2 = (j1 + 1 < T) ? s1 + N : NULL;
+    for (int j = 0; j < R; ++j) {
+      cplx v[32];
+      for (int r = 0; r < P1; ++r) v[r] = data[(size_t)r * R + j];
+      col_twiddle(v, P1, twl[j]);
+      dft_any(v, P1, +1);
+      for (int q = 0; q < P1; ++q) {
+        const int m = j + q * R;
+        const int idx = (m < halfN) ? 2 * m : 2 * (N - 1 - m) + 1;
+        s1[idx] = v[q].x;
+        if (s2) s2[idx] = v[q].y;
+      }
+    }
+  }
+  free(nat);
   free(data);
   free(tw);
   return 0;

@@ -288,6 +288,8 @@ def load_twin() -> ctypes.CDLL:
         lib.em_twin_rows.argtypes = [ctypes.c_int, ctypes.c_double, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, ctypes.c_int,
                                      ctypes.c_int, ctypes.c_int, ctypes.c_int, c_dp, c_dp]
         lib.em_twin_rows.restype = ctypes.c_int
+        lib.em_twin_long_pow2.argtypes = [ctypes.c_int, ctypes.c_double, c_dp, c_dp, c_dp, c_dp, ctypes.c_int, c_dp, c_dp]
+        lib.em_twin_long_pow2.restype = ctypes.c_int
         _twin = lib
     return _twin
 
@@ -324,4 +326,15 @@ def twin_bluestein(N: int, a: float, lam, W, pre, post, hhat, ts, twl=None, lr: 
                                       int(rows), int(bool(long_path)), len(ts), _dp(ts), _dp(out))
     if rc:
         raise ValueError(f"em_twin bluestein rc={rc}")
+    return out
+
+
+def twin_long_pow2(N: int, a: float, lam, W, pre, twl, ts) -> np.ndarray:
+    """Stress [T, N] of a power-of-two line above 8192 nodes exactly as the GPU's scatter / row / column kernels compute it."""
+    c = lambda x: np.ascontiguousarray(x, dtype=np.float64)
+    lam, W, pre, twl, ts = c(lam), c(W), c(pre), c(twl), c(np.atleast_1d(ts))
+    out = np.empty((len(ts), N), dtype=np.float64)
+    rc = load_twin().em_twin_long_pow2(int(N), float(a), _dp(lam), _dp(W), _dp(pre), _dp(twl), len(ts), _dp(ts), _dp(out))
+    if rc:
+        raise ValueError(f"em_twin_long_pow2 rc={rc}")
     return out

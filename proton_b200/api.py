@@ -305,7 +305,7 @@ class Plan:
     def debug_table(self, line: int, which: str) -> np.ndarray:
         """Test hook: one of the device tables the kernels read for `line` (float64; complex tables interleaved)."""
         N = int(self.node_off[line + 1] - self.node_off[line])
-        out = np.empty(max(4 * N + 8, 2 * 131072 + 8), dtype=np.float64)
+        out = np.empty(max(4 * N + 8, 2 * 131072 + 8), dtype=np.float64)      # (H of the longest class: 131072 complex)
         n = ctypes.c_int64()
         check(self.ctx._lib.proton_em_debug_line_table(self._h, int(line), self.TABLES[which], out.ctypes.data, out.size,
                                                        ctypes.byref(n)))

@@ -112,3 +112,27 @@ def test_long_lines_equal_the_cpu_twin_bit_for_bit(oracle):
         plan.close()
     finally:
         ctx.close()
+
+
+def test_long_power_of_two_lines_equal_the_cpu_twin_bit_for_bit(oracle):
+    """N = 16384 ... 131072: scatter kernel, inverse-only row pass, column pass without chirps — the last class."""
+    from proton_b200.api import Context
+    rng = np.random.default_rng(10)
+    sizes = [16384, 32768, 65536, 131072]
+    batch = synth_batch(rng, sizes)
+    ts = TS[:3]
+    ctx = Context(0)
+    try:
+        plan = ctx.pack(batch)
+        got = plan.eval(ts, critical=40e6)
+        for l, n in enumerate(sizes):
+            t = {k: plan.debug_table(l, k) for k in ("lambda", "W", "pre", "twl")}
+            want = oracle.twin_long_pow2(n, float(batch.a_coeff[l]), t["lambda"], t["W"], t["pre"], t["twl"], ts)
+            g = got.line(l)
+            same = g.view(np.uint64) == want.view(np.uint64)
+            assert same.all(), (f"N={n}: {np.count_nonzero(~same)} of {same.size} values differ, "
+                                f"worst {np.abs(g - want).max() / np.abs(want).max():.3e}")
+            assert np.array_equal(got.max_stress[l], want.max(axis=1)) and np.array_equal(got.argmax[l], want.argmax(axis=1))
+        plan.close()
+    finally:
+        ctx.close()
