@@ -467,3 +467,37 @@ def test_zz_near_tie_escapes_stay_within_the_committed_bounds():
     # measured on B200 this round: 0 arg-max and 0 flag escapes in 14 512 rows
     assert ESC.argmax <= 2, ESC
     assert ESC.flag <= 1, ESC
+
+
+def test_kernels_write_nothing_outside_their_output_buffers(ctx):
+    """Guard bands of a sentinel value around every output array (stress, max, argmax, flag), for a batch that goes
+    through every kernel family, with and without an initial stress: the bands must come back untouched."""
+    import torch
+    rng = np.random.default_rng(77)
+    sizes = [1, 2, 5, 33, 64, 88, 100, 257, 300, 330, 513, 600, 700, 1024, 1100, 1300, 2049, 2500, 2600, 3000, 3500,
+             4096, 4097, 5000, 8192, 12001, 16384]
+    batch = synth_batch(rng, sizes)
+    ts = np.logspace(6, np.log10(6.38e8), 5)                   # odd count: the last transform carries one timestamp
+    dev = torch.device("cuda:0")
+    tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    d_in = [tt(x) for x in (batch.num_nodes, batch.a_coeff, batch.trip_off, batch.trip_row, batch.trip_col, batch.trip_val,
+                            batch.u_off, batch.curden)]
+    L, T, G = batch.num_lines, len(ts), 4096
+    n_st, n_lt = batch.total_nodes * T, L * T
+    s0 = 1e7 * rng.normal(size=batch.total_nodes)
+    for sigma0 in (None, s0):
+        stress = torch.full((n_st + 2 * G,), 12345.0, dtype=torch.float64, device=dev)
+        mx = torch.full((n_lt + 2 * G,), 12345.0, dtype=torch.float64, device=dev)
+        amx = torch.full((n_lt + 2 * G,), -7, dtype=torch.int32, device=dev)
+        flag = torch.full((n_lt + 2 * G,), 99, dtype=torch.uint8, device=dev)
+        plan = ctx.pack_device(*d_in) if sigma0 is None else ctx.pack(batch, sigma0=sigma0)
+        plan.eval_device(tt(ts), stress[G:G + n_st], mx[G:G + n_lt], amx[G:G + n_lt], flag[G:G + n_lt], critical=40e6)
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        for buf, val in ((stress, 12345.0), (mx, 12345.0), (amx, -7), (flag, 99)):
+            assert bool((buf[:G] == val).all()) and bool((buf[-G:] == val).all())
+        body = stress[G:G + n_st]
+        assert bool(torch.isfinite(body).all()) and not bool((body == 12345.0).any())       # every value was written
+        assert not bool((mx[G:G + n_lt] == 12345.0).any()) and not bool((amx[G:G + n_lt] == -7).any())
+        assert not bool((flag[G:G + n_lt] == 99).any())
+        plan.close()
