@@ -321,7 +321,7 @@ struct proton_em_plan {
   std::vector<int> h_class_lines;    // host copy of d_class_lines
   // long-line transform lists (slot -> line, timestamp pair): they depend on (T, chunk range) only, so they are
   // built and uploaded once and reused by every later evaluation of the plan
-  struct LongList { int T, c0, c1; long long n; DevBuf<em::SlotRec> recs; };
+  struct LongList { int T, c0, c1; long long n; DevBuf<em::SlotRec> recs; std::vector<em::SlotRec> host; };
   std::vector<LongList*> long_lists;
   std::vector<long long> node_off;   // host copy
   std::vector<int> num_nodes;        // host copy
@@ -1215,8 +1215,20 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
   for (auto* c : p->long_lists)
     if (c->T == T && c->c0 == chunk_begin && c->c1 == chunk_end) { ll = c; break; }
   if (!ll) {
-    // one record per transform slot (line-major, timestamp pairs of a line consecutive)
-    std::vector<em::SlotRec> recs((size_t)n_tr_total);
+    // one record per transform slot (line-major, timestamp pairs of a line consecutive); the host copy lives as long
+    // as the list, so the upload needs no synchronisation
+    if (p->long_lists.size() >= 8) {            // a plan evaluated at many different T: drop the oldest list
+      CU_TRY(cudaStreamSynchronize(ctx->stream));
+      proton_em_plan::LongList* old = p->long_lists.front();
+      p->long_lists.erase(p->long_lists.begin());
+      old->recs.free();
+      delete old;
+    }
+    ll = new proton_em_plan::LongList();
+    ll->T = T; ll->c0 = chunk_begin; ll->c1 = chunk_end; ll->n = n_tr_total;
+    p->long_lists.push_back(ll);
+    std::vector<em::SlotRec>& recs = ll->host;
+    recs.resize((size_t)n_tr_total);
     size_t o = 0;
     for (const auto* cl : longs)
       for (int i = 0; i < cl->count; ++i) {
@@ -1231,18 +1243,8 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
           r.N = N; r.line = line; r.pair = pr; r.reserved = 0;
         }
       }
-    if (p->long_lists.size() >= 8) {            // a plan evaluated at many different T: drop the oldest list
-      proton_em_plan::LongList* old = p->long_lists.front();
-      p->long_lists.erase(p->long_lists.begin());
-      old->recs.free();                         // stream-ordered: earlier evaluations on ctx->stream are done with it
-      delete old;
-    }
-    ll = new proton_em_plan::LongList();
-    ll->T = T; ll->c0 = chunk_begin; ll->c1 = chunk_end; ll->n = n_tr_total;
-    p->long_lists.push_back(ll);
     CU_TRY(ll->recs.alloc((size_t)n_tr_total));
     CU_TRY(cudaMemcpyAsync(ll->recs.p, recs.data(), n_tr_total * sizeof(em::SlotRec), cudaMemcpyHostToDevice, ctx->stream));
-    CU_TRY(cudaStreamSynchronize(ctx->stream));   // `recs` is pageable host memory that goes away at the end of this block
   }
   *list_out = ll;
   // fork: the lanes start after everything queued so far on the main stream (uploads above included)
