@@ -103,6 +103,11 @@ int proton_em_pack_sigma0(proton_em_ctx* ctx, const proton_em_batch* batch, cons
 int proton_em_plan_destroy(proton_em_plan* plan);
 int64_t proton_em_plan_total_nodes(const proton_em_plan* plan);
 int64_t proton_em_plan_num_lines(const proton_em_plan* plan);
+int32_t proton_em_plan_line_nodes(const proton_em_plan* plan, int64_t line);   /* N of one line; 0 if out of range */
+/* Optional line names (the reference identifies a line by the stem of its csv, PROTON_cli.py:993): the plan copies
+ * the n = num_lines strings; proton_em_plan_line_name returns NULL for a plan without names or a line out of range. */
+int proton_em_plan_set_line_names(proton_em_plan* plan, const char* const* names, int64_t n);
+const char* proton_em_plan_line_name(const proton_em_plan* plan, int64_t line);
 /* Device scratch the plan holds (bytes) — modal weights, packed r, per-line tables. */
 int64_t proton_em_plan_scratch_bytes(const proton_em_plan* plan);
 
@@ -160,6 +165,17 @@ int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_
  * the reference's stdout text of the first failure. */
 int proton_em_run_cfgs(proton_em_ctx* ctx, const char* const* cfg_paths, int64_t n, int32_t* status, char* msg,
                        size_t msg_len);
+
+/* Convenience: pack every discretised line of a PROTON project directory in one plan.  For every sub-directory
+ * <project_dir>/input/<line>/<variant>/ — variant = "<technology>_<temperature>_<width>" as the reference composes it
+ * (analytical_class_cli.py:30, e.g. "CuDD_378.0_0.1"); NULL or "" = the first variant, in byte order, that holds an
+ * analytical.txt — reads what Matrix_Formulation_Class wrote there (matrix_formulation_func_cli.py:240-286):
+ * analytical.txt (nx_total, Acoef; read like analytical_class_cli.py:31-41), B.csv and curden.csv (read like
+ * proton_em_run_cfg reads them).  Lines are taken in byte order of their directory names, which become the plan's
+ * line names.  A line whose files are missing or inconsistent is left out and counted in *skipped (may be NULL); `msg`
+ * receives the text of the first such failure.  Returns PROTON_EM_EIO if no line could be read. */
+int proton_em_pack_from_project(proton_em_ctx* ctx, const char* project_dir, const char* variant,
+                                proton_em_plan** out, int64_t* skipped, char* msg, size_t msg_len);
 
 /* One line with no allocation anywhere (this entry point has no counterpart in the reference, which
  * allocates freely inside its own process).  It exists for callers that must not ask the CUDA runtime for

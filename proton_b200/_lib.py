@@ -48,7 +48,9 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_plan_scratch_bytes", "proton_em_eval", "proton_em_synchronize", "proton_em_stream",
            "proton_em_launch_count", "proton_em_analyze_host", "proton_em_run_cfg", "proton_em_debug_exp",
            "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read",
-           "proton_em_analyze_history_host", "proton_em_debug_line_table", "proton_em_pack_sigma0", "proton_em_run_cfgs"]
+           "proton_em_analyze_history_host", "proton_em_debug_line_table", "proton_em_pack_sigma0", "proton_em_run_cfgs",
+           "proton_em_pack_from_project", "proton_em_plan_line_nodes", "proton_em_plan_set_line_names",
+           "proton_em_plan_line_name"]
 
 
 def load() -> ctypes.CDLL:
@@ -83,6 +85,14 @@ def load() -> ctypes.CDLL:
     if hasattr(lib, "proton_em_run_cfgs"):
         lib.proton_em_run_cfgs.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p), ctypes.c_int64, c_i32p, ctypes.c_char_p,
                                            ctypes.c_size_t]
+    if hasattr(lib, "proton_em_pack_from_project"):
+        lib.proton_em_pack_from_project.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.POINTER(vp),
+                                                    ctypes.POINTER(ctypes.c_int64), ctypes.c_char_p, ctypes.c_size_t]
+        lib.proton_em_plan_line_nodes.argtypes = [vp, ctypes.c_int64]
+        lib.proton_em_plan_line_nodes.restype = ctypes.c_int32
+        lib.proton_em_plan_set_line_names.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p), ctypes.c_int64]
+        lib.proton_em_plan_line_name.argtypes = [vp, ctypes.c_int64]
+        lib.proton_em_plan_line_name.restype = ctypes.c_char_p
     lib.proton_em_debug_exp.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_debug_expm1.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_eval_line_noalloc.argtypes = [ctypes.c_int, vp, ctypes.c_int32, ctypes.c_double, ctypes.c_int32, vp, vp,

@@ -8,6 +8,7 @@ device (torch CUDA tensor) entry points are separate so nothing is copied behind
 from __future__ import annotations
 
 import ctypes
+import os
 import weakref
 from dataclasses import dataclass
 from typing import Iterable, Optional, Sequence
@@ -181,6 +182,25 @@ class Context:
             check(self._lib.proton_em_pack_sigma0(self._h, ctypes.byref(cb), s0.ctypes.data, HOST, ctypes.byref(h)))
         return Plan(self, h, batch.node_off, keep=None)
 
+    def pack_project(self, project_dir: str, variant: Optional[str] = None) -> "Plan":
+        """Every discretised line of a PROTON project directory (`<project>/input/<line>/<variant>/analytical.txt,
+        B.csv, curden.csv`) in one plan, read and parsed inside the library; see proton_em_pack_from_project.
+        `plan.names` are the line names, `plan.skipped` the number of lines left out, `plan.message` the text of the
+        first failure."""
+        h, skipped = ctypes.c_void_p(), ctypes.c_int64()
+        msg = ctypes.create_string_buffer(1024)
+        rc = self._lib.proton_em_pack_from_project(self._h, os.fsencode(project_dir),
+                                                   variant.encode() if variant else None, ctypes.byref(h),
+                                                   ctypes.byref(skipped), msg, len(msg))
+        if rc:
+            raise ProtonEmError(rc, msg.value.decode(errors="replace").strip())
+        L = int(self._lib.proton_em_plan_num_lines(h))
+        node_off = np.zeros(L + 1, dtype=np.int64)
+        np.cumsum([self._lib.proton_em_plan_line_nodes(h, l) for l in range(L)], out=node_off[1:])
+        plan = Plan(self, h, node_off, keep=None)
+        plan.skipped, plan.message = int(skipped.value), msg.value.decode(errors="replace")
+        return plan
+
     def pack_device(self, num_nodes, a_coeff, trip_off, trip_row, trip_col, trip_val, u_off, curden) -> "Plan":
         """All arguments are torch CUDA tensors (int32 / float64 / int64 as in proton_em_batch); the plan keeps
         references to them because the kernels read num_nodes / a_coeff / trip_off in place."""
@@ -287,6 +307,19 @@ class Plan:
     @property
     def scratch_bytes(self) -> int:
         return int(self.ctx._lib.proton_em_plan_scratch_bytes(self._h))
+
+    @property
+    def names(self) -> Optional[list]:
+        """Line names held by the plan (proton_em_plan_set_line_names / pack_project), or None."""
+        first = self.ctx._lib.proton_em_plan_line_name(self._h, 0)
+        if first is None:
+            return None
+        return [self.ctx._lib.proton_em_plan_line_name(self._h, l).decode() for l in range(self.num_lines)]
+
+    @names.setter
+    def names(self, names) -> None:
+        arr = (ctypes.c_char_p * len(names))(*[str(n).encode() for n in names])
+        check(self.ctx._lib.proton_em_plan_set_line_names(self._h, arr, len(names)))
 
     def close(self):
         if self._h:

@@ -326,6 +326,7 @@ struct proton_em_plan {
   std::vector<long long> node_off;   // host copy
   std::vector<int> num_nodes;        // host copy
   std::vector<double> a_host;        // host copy of a_coeff
+  std::vector<std::string> names;    // optional line names (proton_em_plan_set_line_names / proton_em_pack_from_project)
 };
 
 namespace {
@@ -958,6 +959,21 @@ int proton_em_plan_destroy(proton_em_plan* plan) {
 }
 int64_t proton_em_plan_total_nodes(const proton_em_plan* plan) { return plan ? plan->total_nodes : 0; }
 int64_t proton_em_plan_num_lines(const proton_em_plan* plan) { return plan ? plan->L : 0; }
+int32_t proton_em_plan_line_nodes(const proton_em_plan* plan, int64_t line) {
+  return (plan && line >= 0 && line < plan->L) ? plan->num_nodes[(size_t)line] : 0;
+}
+int proton_em_plan_set_line_names(proton_em_plan* plan, const char* const* names, int64_t n) {
+  if (!plan) return fail(PROTON_EM_EINVAL, "proton_em_plan_set_line_names: null plan");
+  if (n != plan->L || (n > 0 && !names)) return fail(PROTON_EM_EINVAL, "proton_em_plan_set_line_names: the plan has %lld lines, %lld names given", (long long)plan->L, (long long)n);
+  std::vector<std::string> v((size_t)n);
+  for (int64_t i = 0; i < n; ++i) v[(size_t)i] = names[i] ? names[i] : "";
+  plan->names.swap(v);
+  return PROTON_EM_OK;
+}
+const char* proton_em_plan_line_name(const proton_em_plan* plan, int64_t line) {
+  if (!plan || line < 0 || (size_t)line >= plan->names.size()) return nullptr;
+  return plan->names[(size_t)line].c_str();
+}
 int64_t proton_em_plan_scratch_bytes(const proton_em_plan* p) {
   if (!p) return 0;
   return (int64_t)(p->d_node_off.bytes() + p->d_r_idx.bytes() + p->d_r_cnt.bytes() + p->d_line_tab.bytes() +

@@ -1,5 +1,6 @@
 // proton_em_cfg.cpp — Level-1 entry points: what the reference PROCESS does for one analytical.cfg (proton_em_run_cfg),
-// and the same for many cfgs in one batched evaluation (proton_em_run_cfgs).
+// the same for many cfgs in one batched evaluation (proton_em_run_cfgs), and the packing of a whole project directory
+// from the files the reference's formulation wrote (proton_em_pack_from_project).
 //
 // Mirrors main / simulation_engine::read_file / analyical_wrapper / tripletParser of the reference
 // binary (bin/EMtool_analytical@0x6920, @0xaaf4, @0xb93c, @0xb010), including
@@ -12,14 +13,18 @@
 //   * an input_files path that does not contain "input".
 #include "../../include/proton_em.h"
 
+#include <algorithm>
+#include <atomic>
 #include <cerrno>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <dirent.h>
 #include <fstream>
 #include <sstream>
 #include <string>
 #include <sys/stat.h>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -66,39 +71,14 @@ struct CfgLine {
   std::vector<double> vals;
 };
 
-// read_file + the reading half of analyical_wrapper; on failure `text` is what the reference prints before exit(1).
-int read_cfg_line(const char* cfg_path, CfgLine& out, std::string& text) {
-  if (!cfg_path) { text = "Wrong number of arguments. Configuration file expected.\n"; return PROTON_EM_EINVAL; }
-  // ---- read_file: "key value" per line, later keys override, unknown keys ignored -----------------
-  std::string input_files;
-  long num_nodes = 0;
-  double a_coeff = 0.0, sim_time = 0.0;
-  bool have_in = false, have_n = false, have_a = false, have_t = false;
-  {
-    std::ifstream f(cfg_path);
-    std::string line;
-    while (f && std::getline(f, line)) {
-      std::istringstream is(line);
-      std::string key;
-      if (!(is >> key)) continue;
-      if (key == "input_files") { std::string v; if (is >> v) { input_files = v; have_in = true; } }
-      else if (key == "num_nodes") { long v; if (is >> v) { num_nodes = v; have_n = true; } }
-      else if (key == "A_coeff") { double v; if (is >> v) { a_coeff = v; have_a = true; } }
-      else if (key == "simulation_time") { double v; if (is >> v) { sim_time = v; have_t = true; } }
-    }
-  }
-  if (!have_in) { text = std::string(cfg_path) + " The configuration file does not include the input directory.\n"; return PROTON_EM_EINVAL; }
-  if (!have_n) { text = "The configuration file does not include the number of nodes.\n"; return PROTON_EM_EINVAL; }
-  if (!have_a) { text = "The configuration file does not include the A coefficient.\n"; return PROTON_EM_EINVAL; }
-  if (!have_t) { text = "The configuration file does not include the target simulation time.\n"; return PROTON_EM_EINVAL; }
-  if (num_nodes <= 0 || num_nodes > 0x7fffffffL) { text = "num_nodes must be a positive 32-bit integer.\n"; return PROTON_EM_EINVAL; }
-
-  // ---- analyical_wrapper: output directory, curden.csv, B.csv ------------------------------------
+// The reading half of analyical_wrapper: output directory, curden.csv, B.csv of the directory `input_files` (with its
+// trailing '/'); out.N must be set.  On failure `text` is what the reference prints before exit(1).
+int read_line_files(const std::string& input_files, CfgLine& out, std::string& text) {
+  const long num_nodes = out.N;
   const size_t pos = input_files.find("input");
   if (pos == std::string::npos) { text = "The input directory path does not contain \"input\".\n"; return PROTON_EM_EINVAL; }
   out.out_dir = input_files;
   out.out_dir.replace(pos, 5, "output");
-  out.N = (int32_t)num_nodes; out.a_coeff = a_coeff; out.sim_time = sim_time;
   {
     const std::string path = input_files + "curden.csv";
     std::ifstream f(path);
@@ -146,6 +126,38 @@ int read_cfg_line(const char* cfg_path, CfgLine& out, std::string& text) {
     }
   }
   return PROTON_EM_OK;
+}
+
+
+// read_file + the reading half of analyical_wrapper; on failure `text` is what the reference prints before exit(1).
+int read_cfg_line(const char* cfg_path, CfgLine& out, std::string& text) {
+  if (!cfg_path) { text = "Wrong number of arguments. Configuration file expected.\n"; return PROTON_EM_EINVAL; }
+  // ---- read_file: "key value" per line, later keys override, unknown keys ignored -----------------
+  std::string input_files;
+  long num_nodes = 0;
+  double a_coeff = 0.0, sim_time = 0.0;
+  bool have_in = false, have_n = false, have_a = false, have_t = false;
+  {
+    std::ifstream f(cfg_path);
+    std::string line;
+    while (f && std::getline(f, line)) {
+      std::istringstream is(line);
+      std::string key;
+      if (!(is >> key)) continue;
+      if (key == "input_files") { std::string v; if (is >> v) { input_files = v; have_in = true; } }
+      else if (key == "num_nodes") { long v; if (is >> v) { num_nodes = v; have_n = true; } }
+      else if (key == "A_coeff") { double v; if (is >> v) { a_coeff = v; have_a = true; } }
+      else if (key == "simulation_time") { double v; if (is >> v) { sim_time = v; have_t = true; } }
+    }
+  }
+  if (!have_in) { text = std::string(cfg_path) + " The configuration file does not include the input directory.\n"; return PROTON_EM_EINVAL; }
+  if (!have_n) { text = "The configuration file does not include the number of nodes.\n"; return PROTON_EM_EINVAL; }
+  if (!have_a) { text = "The configuration file does not include the A coefficient.\n"; return PROTON_EM_EINVAL; }
+  if (!have_t) { text = "The configuration file does not include the target simulation time.\n"; return PROTON_EM_EINVAL; }
+  if (num_nodes <= 0 || num_nodes > 0x7fffffffL) { text = "num_nodes must be a positive 32-bit integer.\n"; return PROTON_EM_EINVAL; }
+
+  out.N = (int32_t)num_nodes; out.a_coeff = a_coeff; out.sim_time = sim_time;
+  return read_line_files(input_files, out, text);
 }
 
 // stress_<%f>.txt, one "%.18g" per line (the writing half of analyical_wrapper)
@@ -254,4 +266,133 @@ extern "C" int proton_em_run_cfgs(proton_em_ctx* ctx, const char* const* cfg_pat
     }
   }
   return failed;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// proton_em_pack_from_project: every discretised line of a PROTON project directory in one plan.
+// Matrix_Formulation_Class leaves, per line and per (technology, temperature, width) variant, the directory
+//   <project>/input/<line>/<technology>_<temperature>_<width>/{analytical.txt, B.csv, curden.csv}
+// (matrix_formulation_func_cli.py:217-286); Analytical_Class reads nx_total and Acoef from analytical.txt
+// (analytical_class_cli.py:31-41: `words = line.split(); if 'Acoef' in words: Acoef = words[2]`) and the process reads
+// the two csv files.  The files are parsed on a few host threads; the arithmetic starts with proton_em_pack.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+std::vector<std::string> list_dirs(const std::string& path) {
+  std::vector<std::string> out;
+  DIR* d = opendir(path.c_str());
+  if (!d) return out;
+  while (dirent* e = readdir(d)) {
+    const std::string name = e->d_name;
+    if (name == "." || name == "..") continue;
+    struct stat st;
+    if (stat((path + "/" + name).c_str(), &st) == 0 && S_ISDIR(st.st_mode)) out.push_back(name);
+  }
+  closedir(d);
+  std::sort(out.begin(), out.end());
+  return out;
+}
+
+bool file_exists(const std::string& path) {
+  struct stat st;
+  return stat(path.c_str(), &st) == 0 && S_ISREG(st.st_mode);
+}
+
+// analytical.txt: "nx_total = <int>" and "Acoef = <float>", any order, whitespace-separated words
+int read_analytical_txt(const std::string& path, CfgLine& out) {
+  std::ifstream f(path);
+  if (!f) return PROTON_EM_EIO;
+  bool have_n = false, have_a = false;
+  std::string line;
+  while (std::getline(f, line)) {
+    std::istringstream is(line);
+    std::vector<std::string> words;
+    for (std::string w; is >> w;) words.push_back(w);
+    if (words.size() < 3) continue;
+    for (const std::string& w : words) {
+      if (w == "Acoef") { out.a_coeff = std::atof(words[2].c_str()); have_a = true; }
+      if (w == "nx_total") {
+        const long v = std::strtol(words[2].c_str(), nullptr, 10);
+        if (v <= 0 || v > 0x7fffffffL) return PROTON_EM_EINVAL;
+        out.N = (int32_t)v; have_n = true;
+      }
+    }
+  }
+  return (have_n && have_a) ? PROTON_EM_OK : PROTON_EM_EINVAL;
+}
+
+}  // namespace
+
+extern "C" int proton_em_pack_from_project(proton_em_ctx* ctx, const char* project_dir, const char* variant,
+                                           proton_em_plan** out, int64_t* skipped, char* msg, size_t msg_len) {
+  set_msg(msg, msg_len, "");
+  if (skipped) *skipped = 0;
+  if (!out || !project_dir) { set_msg(msg, msg_len, "proton_em_pack_from_project: bad arguments.\n"); return PROTON_EM_EINVAL; }
+  *out = nullptr;
+  if (!ctx) { set_msg(msg, msg_len, "No CUDA context.\n"); return PROTON_EM_ECUDA; }
+  const std::string in_root = std::string(project_dir) + "/input";
+  const std::vector<std::string> line_names = list_dirs(in_root);
+  if (line_names.empty()) {
+    set_msg(msg, msg_len, "No discretization has been performed in " + in_root + ".\n");
+    return PROTON_EM_EIO;
+  }
+  const std::string want = variant ? variant : "";
+  const size_t n = line_names.size();
+  std::vector<CfgLine> lines(n);
+  std::vector<int> rc(n, PROTON_EM_OK);
+  std::vector<std::string> text(n);
+  std::atomic<size_t> next{0};
+  auto work = [&]() {
+    for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
+      const std::string line_dir = in_root + "/" + line_names[i];
+      std::string var = want;
+      if (var.empty()) {
+        for (const std::string& v : list_dirs(line_dir))
+          if (file_exists(line_dir + "/" + v + "/analytical.txt")) { var = v; break; }
+      }
+      const std::string dir = line_dir + "/" + var + "/";
+      if (var.empty() || read_analytical_txt(dir + "analytical.txt", lines[i]) != PROTON_EM_OK) {
+        rc[i] = PROTON_EM_EIO;
+        text[i] = "No discretization has been performed for line " + line_names[i] +
+                  (want.empty() ? std::string(".\n") : " with params: " + want + ".\n");
+        continue;
+      }
+      rc[i] = read_line_files(dir, lines[i], text[i]);
+    }
+  };
+  {
+    unsigned nt = std::thread::hardware_concurrency();
+    nt = nt == 0 ? 1 : (nt > 16 ? 16 : nt);
+    if (nt > n) nt = (unsigned)n;
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < nt; ++t) pool.emplace_back(work);
+    work();
+    for (std::thread& t : pool) t.join();
+  }
+  std::vector<int32_t> nn, rows, cols;
+  std::vector<double> aa, vals, u;
+  std::vector<int64_t> trip_off(1, 0), u_off(1, 0);
+  std::vector<const char*> names;
+  int64_t bad = 0;
+  for (size_t i = 0; i < n; ++i) {
+    if (rc[i] != PROTON_EM_OK) {
+      if (bad++ == 0) set_msg(msg, msg_len, text[i]);
+      continue;
+    }
+    const CfgLine& ln = lines[i];
+    nn.push_back(ln.N); aa.push_back(ln.a_coeff);
+    rows.insert(rows.end(), ln.rows.begin(), ln.rows.end());
+    cols.insert(cols.end(), ln.cols.begin(), ln.cols.end());
+    vals.insert(vals.end(), ln.vals.begin(), ln.vals.end());
+    u.insert(u.end(), ln.u.begin(), ln.u.end());
+    trip_off.push_back((int64_t)rows.size()); u_off.push_back((int64_t)u.size());
+    names.push_back(line_names[i].c_str());
+  }
+  if (skipped) *skipped = bad;
+  if (nn.empty()) return PROTON_EM_EIO;
+  proton_em_batch batch{(int64_t)nn.size(), nn.data(), aa.data(), trip_off.data(), rows.data(), cols.data(), vals.data(),
+                        u_off.data(), u.data()};
+  const int prc = proton_em_pack(ctx, &batch, PROTON_EM_HOST, out);
+  if (prc != PROTON_EM_OK) { set_msg(msg, msg_len, std::string(proton_em_last_error()) + "\n"); return prc; }
+  return proton_em_plan_set_line_names(*out, names.data(), (int64_t)names.size());
 }

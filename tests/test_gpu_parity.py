@@ -372,6 +372,59 @@ def test_many_cfgs_in_one_call_write_the_same_files_as_one_process_each(ctx, ora
         assert len(batched) > 0
 
 
+def test_project_directory_packed_inside_the_library(ctx, oracle, tmp_path):
+    """proton_em_pack_from_project: every line Matrix_Formulation_Class discretised under <project>/input/<line>/<variant>/
+    (analytical.txt, B.csv, curden.csv) becomes one plan, lines in byte order of their names; the result is bit-identical
+    to packing the same inputs through proton_em_pack and within 1e-9 of the oracle; a line with a missing file is left
+    out and counted, the rest of the project still packs."""
+    from proton_b200.api import LineBatch
+    from proton_b200._lib import ProtonEmError
+    rng = np.random.default_rng(1618)
+    proj = tmp_path / "proj"
+    cases = {"M5_n1_7": (300, 4), "M1_n0_2": (1, 1), "M3_n2_9": (1500, 5), "M6_n9_9": (5000, 7), "M2_n1_1": (64, 2)}
+    lines = {}
+    for name, (N, S) in cases.items():
+        li = synth_line(rng, N, S)
+        li.name = name
+        d = proj / "input" / name / "CuDD_378.0_0.1"
+        oracle.write_line_inputs(d, li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, 1e6)
+        (d / "analytical.txt").write_text(f"nx_total = {li.num_nodes}\nAcoef = {li.a_coeff!r}\n")
+        lines[name] = li
+    # a second variant of one line (other width), a line whose B.csv is gone, a line that was never discretised
+    other = synth_line(rng, 90, 3)
+    d2 = proj / "input" / "M5_n1_7" / "CuDD_378.0_0.2"
+    oracle.write_line_inputs(d2, other.num_nodes, other.a_coeff, other.rows, other.cols, other.vals, other.curden, 1e6)
+    (d2 / "analytical.txt").write_text(f"nx_total = {other.num_nodes}\nAcoef = {other.a_coeff!r}\n")
+    gone = synth_line(rng, 40, 2)
+    d3 = proj / "input" / "M4_gone" / "CuDD_378.0_0.1"
+    oracle.write_line_inputs(d3, gone.num_nodes, gone.a_coeff, gone.rows, gone.cols, gone.vals, gone.curden, 1e6)
+    (d3 / "analytical.txt").write_text(f"nx_total = {gone.num_nodes}\nAcoef = {gone.a_coeff!r}\n")
+    (d3 / "B.csv").unlink()
+    (proj / "input" / "M9_never").mkdir()
+    ts = np.array([1e6, 1e7, 6.38e8])
+    for variant in ("CuDD_378.0_0.1", None):
+        plan = ctx.pack_project(str(proj), variant)
+        assert plan.names == sorted(cases) and plan.skipped == 2
+        assert "B.csv was not found" in plan.message
+        got = plan.eval(ts, critical=40e6)
+        ordered = [lines[n] for n in sorted(cases)]
+        direct = ctx.analyze_host(LineBatch.from_lines(ordered), ts, critical=40e6)
+        assert np.array_equal(got.stress, direct.stress) and np.array_equal(got.max_stress, direct.max_stress)
+        assert np.array_equal(got.argmax, direct.argmax) and np.array_equal(got.flag, direct.flag)
+        for l, li in enumerate(ordered):
+            want, _, _ = oracle.line(li.num_nodes, li.a_coeff, li.rows, li.cols, li.vals, li.curden, ts)
+            assert np.abs(got.line(l) - want).max() <= 1e-9 * np.abs(want).max()
+        plan.close()
+    plan = ctx.pack_project(str(proj), "CuDD_378.0_0.2")            # only one line has this variant
+    assert plan.names == ["M5_n1_7"] and plan.skipped == 6 and plan.total_nodes == 90
+    assert "No discretization has been performed for line M1_n0_2 with params: CuDD_378.0_0.2" in plan.message
+    plan.names = ["renamed"]
+    assert plan.names == ["renamed"]
+    plan.close()
+    with pytest.raises(ProtonEmError):
+        ctx.pack_project(str(tmp_path / "nowhere"))
+
+
 def test_batched_analyze_driver_and_launcher_class(ctx, oracle, ibmpg1_lines, tmp_path):
     """the batch-aware `analyze` (project directory in, problematic lines out, reference-format
     stress files on request) and the in-process `Analytical_Class`."""
