@@ -177,6 +177,38 @@ int proton_em_run_cfgs(proton_em_ctx* ctx, const char* const* cfg_paths, int64_t
 int proton_em_pack_from_project(proton_em_ctx* ctx, const char* project_dir, const char* variant,
                                 proton_em_plan** out, int64_t* skipped, char* msg, size_t msg_len);
 
+/* The discretiser of a whole grid in one host call: what Matrix_Formulation_Class.matrix_formulation
+ * does per line in step mode (matrix_formulation_func_cli.py:24-299) with the step policy of PROTON_cli.analyze_line_item
+ * (PROTON_cli.py:1000-1014), over a flat table of segments.  Host arithmetic only — needs no context and no GPU — and
+ * bit-identical to the Python formulation (proton_b200/formulation.py); its outputs are the arrays of proton_em_batch.
+ *   seg_off [L+1]     segments of line l are [seg_off[l], seg_off[l+1]), in file order
+ *   length_um, current [K]   columns 3 and 4 of the line's csv rows (um, A)
+ *   lcoord, rcoord [K][2]    integer ids of left_node.split("_")[1], [2] and of the right node's (equal id <=> equal
+ *                            string: the reference compares the strings, :148-157)
+ *   named [K]         both node names non-empty (the reference's truthiness test, :148) */
+typedef struct proton_em_segments {
+  int64_t num_lines;
+  const int64_t* seg_off;
+  const double* length_um;
+  const double* current;
+  const int64_t* lcoord;
+  const int64_t* rcoord;
+  const uint8_t* named;
+} proton_em_segments;
+#define PROTON_EM_FORM_CORRUPT 1     /* "Corrupted CSV segments file." (a line without segments or without nodes) */
+#define PROTON_EM_FORM_NOT_DENSE 2   /* "The given discretization is not dense enough for the geometry of the given line." */
+#define PROTON_EM_FORM_INDEX 3       /* a via before the first node: Python's negative list index; use the Python twin */
+/* step_um: one step per line in um, or NULL for the whole-grid policy 0.99 x the line's shortest segment.  kappa, b:
+ * technology constants (:48-73); width2 = (width * 1e-6)^2 as the reference forms it.  Outputs (caller-allocated):
+ * num_nodes, a_coeff [L]; trip_off [L+1]; trip_row, trip_col, trip_val with room for 2 K entries (a line has at most two
+ * per segment); curden [K] (float32-rounded; u_off of the batch = seg_off).  Returns 0, a PROTON_EM_FORM_* code with
+ * *bad_line (may be NULL) = the first offending line — the batch fails as a whole, nothing usable is written — or
+ * PROTON_EM_EINVAL. */
+int proton_em_formulate_segments(const proton_em_segments* table, const double* step_um, double kappa, double b,
+                                 double width2, int32_t* num_nodes, double* a_coeff, int64_t* trip_off,
+                                 int32_t* trip_row, int32_t* trip_col, double* trip_val, double* curden,
+                                 int64_t* bad_line);
+
 /* One line with no allocation anywhere (this entry point has no counterpart in the reference, which
  * allocates freely inside its own process).  It exists for callers that must not ask the CUDA runtime for
  * memory: hosts that gave all device memory to their own pool, plug-ins called where cudaMalloc would stall

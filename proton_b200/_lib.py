@@ -25,6 +25,15 @@ class Batch(ctypes.Structure):
                 ("trip_val", ctypes.c_void_p), ("u_off", ctypes.c_void_p), ("curden", ctypes.c_void_p)]
 
 
+class Segments(ctypes.Structure):          # proton_em_segments
+    _fields_ = [("num_lines", ctypes.c_int64), ("seg_off", ctypes.c_void_p), ("length_um", ctypes.c_void_p),
+                ("current", ctypes.c_void_p), ("lcoord", ctypes.c_void_p), ("rcoord", ctypes.c_void_p),
+                ("named", ctypes.c_void_p)]
+
+
+FORM_CORRUPT, FORM_NOT_DENSE, FORM_INDEX = 1, 2, 3
+
+
 class Opts(ctypes.Structure):
     _fields_ = [("critical_stress", ctypes.c_double), ("algorithm", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
@@ -50,7 +59,7 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read",
            "proton_em_analyze_history_host", "proton_em_debug_line_table", "proton_em_pack_sigma0", "proton_em_run_cfgs",
            "proton_em_pack_from_project", "proton_em_plan_line_nodes", "proton_em_plan_set_line_names",
-           "proton_em_plan_line_name"]
+           "proton_em_plan_line_name", "proton_em_formulate_segments"]
 
 
 def load() -> ctypes.CDLL:
@@ -93,6 +102,10 @@ def load() -> ctypes.CDLL:
         lib.proton_em_plan_set_line_names.argtypes = [vp, ctypes.POINTER(ctypes.c_char_p), ctypes.c_int64]
         lib.proton_em_plan_line_name.argtypes = [vp, ctypes.c_int64]
         lib.proton_em_plan_line_name.restype = ctypes.c_char_p
+    if hasattr(lib, "proton_em_formulate_segments"):
+        lib.proton_em_formulate_segments.argtypes = [ctypes.POINTER(Segments), vp, ctypes.c_double, ctypes.c_double,
+                                                     ctypes.c_double, vp, vp, vp, vp, vp, vp, vp,
+                                                     ctypes.POINTER(ctypes.c_int64)]
     lib.proton_em_debug_exp.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_debug_expm1.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_eval_line_noalloc.argtypes = [ctypes.c_int, vp, ctypes.c_int32, ctypes.c_double, ctypes.c_int32, vp, vp,

@@ -250,11 +250,18 @@ class SegmentTable:
         return SegmentTable(names, seg_off, length, current, lc, rc, named)
 
 
-def formulate_table(tab: SegmentTable, *, sp_step=None, technology="CuDD", temperature=378.0, givenWidth=0.1):
-    """Discretise every line of `tab` in step mode, vectorised over all segments; returns a `proton_b200.api.LineBatch`
+def formulate_table(tab: SegmentTable, *, sp_step=None, technology="CuDD", temperature=378.0, givenWidth=0.1,
+                    engine: str = "native"):
+    """Discretise every line of `tab` in step mode in one pass over all segments; returns a `proton_b200.api.LineBatch`
     whose arrays are bit-identical to running `formulate_segments` line by line (same N, Acoef, B triplets in the
     same order, float32-rounded currents).  `sp_step`: one step in um for all lines, an array with one per line, or
-    None for the whole-grid driver's policy 0.99 x the line's shortest segment (PROTON_cli.py:1005-1012)."""
+    None for the whole-grid driver's policy 0.99 x the line's shortest segment (PROTON_cli.py:1005-1012).
+    `engine`: "native" = proton_em_formulate_segments of libproton_em.so (host code, no GPU needed; 0.2 us per line),
+    "numpy" = the same in NumPy array operations (2.6 us per line; the cross-check of tests/test_formulation.py)."""
+    if engine == "native":
+        return _formulate_table_native(tab, sp_step, technology, temperature, givenWidth)
+    if engine != "numpy":
+        raise ValueError("engine must be 'native' or 'numpy'")
     from .api import LineBatch
     kappa, b = technology_constants(technology, temperature)
     L, K = tab.num_lines, len(tab.length_um)
@@ -348,3 +355,39 @@ def formulate_table(tab: SegmentTable, *, sp_step=None, technology="CuDD", tempe
     np.cumsum(np.bincount(a_line, minlength=L), out=trip_off[1:])
     return LineBatch(N.astype(np.int32), acoef, trip_off, a_i.astype(np.int32), a_j.astype(np.int32),
                      a_v * bcoef[a_line], tab.seg_off.copy(), curden, names=list(tab.names))
+
+
+def _formulate_table_native(tab: SegmentTable, sp_step, technology, temperature, givenWidth):
+    """formulate_table through the C ABI (include/proton_em.h: proton_em_formulate_segments)."""
+    import ctypes
+    from . import _lib
+    from .api import LineBatch
+    lib = _lib.load()
+    kappa, b = technology_constants(technology, temperature)
+    L, K = tab.num_lines, len(tab.length_um)
+    c = lambda a, dt: np.ascontiguousarray(a, dtype=dt)
+    seg_off, length_um, current = c(tab.seg_off, np.int64), c(tab.length_um, np.float64), c(tab.current, np.float64)
+    lcoord, rcoord, named = c(tab.lcoord, np.int64), c(tab.rcoord, np.int64), c(tab.named, np.uint8)
+    step = None if sp_step is None else np.broadcast_to(np.asarray(sp_step, dtype=np.float64), (L,)).copy()
+    w = float(givenWidth)
+    segs = _lib.Segments(L, seg_off.ctypes.data, length_um.ctypes.data, current.ctypes.data, lcoord.ctypes.data,
+                         rcoord.ctypes.data, named.ctypes.data)
+    num_nodes, a_coeff = np.empty(max(L, 1), np.int32), np.empty(max(L, 1), np.float64)
+    trip_off = np.zeros(L + 1, np.int64)
+    rows, cols, vals = np.empty(2 * K + 2, np.int32), np.empty(2 * K + 2, np.int32), np.empty(2 * K + 2, np.float64)
+    curden = np.empty(max(K, 1), np.float64)
+    bad = ctypes.c_int64(-1)
+    rc = lib.proton_em_formulate_segments(ctypes.byref(segs), None if step is None else step.ctypes.data, kappa, b,
+                                          w * 1e-6 * w * 1e-6, num_nodes.ctypes.data, a_coeff.ctypes.data,
+                                          trip_off.ctypes.data, rows.ctypes.data, cols.ctypes.data, vals.ctypes.data,
+                                          curden.ctypes.data, ctypes.byref(bad))
+    if rc == _lib.FORM_INDEX:        # Python's negative list indices: only the NumPy formulation reproduces them
+        return formulate_table(tab, sp_step=sp_step, technology=technology, temperature=temperature,
+                               givenWidth=givenWidth, engine="numpy")
+    if rc == _lib.FORM_NOT_DENSE:
+        raise FormulationError(NOT_DENSE_MSG)
+    if rc != 0:
+        raise FormulationError(CORRUPT_MSG)
+    n = int(trip_off[L])
+    return LineBatch(num_nodes[:L], a_coeff[:L], trip_off, rows[:n].copy(), cols[:n].copy(), vals[:n].copy(),
+                     seg_off.copy(), curden[:K], names=list(tab.names))

@@ -74,7 +74,8 @@ def _same_batch(a, b):
         assert np.array_equal(getattr(a, f), getattr(b, f)), f
 
 
-def test_vectorised_discretiser_equals_the_per_line_twin_on_ibmpg1():
+@pytest.mark.parametrize("engine", ["native", "numpy"])
+def test_vectorised_discretiser_equals_the_per_line_twin_on_ibmpg1(engine):
     """formulate_table (all lines at once) against formulate_segments line by line: the analyze
     policy step and several fixed steps, including coarse ones where segments get one point and vias collide with the
     first / last entry of B."""
@@ -83,20 +84,21 @@ def test_vectorised_discretiser_equals_the_per_line_twin_on_ibmpg1():
     lines = W.ibmpg1_segments()
     tab = F.SegmentTable.from_lines(lines)
     assert tab.num_lines == 1717
-    got = F.formulate_table(tab)
+    got = F.formulate_table(tab, engine=engine)
     want = LineBatch.from_lines([F.formulate_segments(s, sp_step=F.analyze_policy_step(s), name=n) for n, s in lines])
     _same_batch(got, want)
     assert got.names == want.names
     for step in (0.5, 2.0, 5.0):
         ok = [(n, s) for n, s in lines if min(x[2] for x in s) >= step]
-        got = F.formulate_table(F.SegmentTable.from_lines(ok), sp_step=step)
+        got = F.formulate_table(F.SegmentTable.from_lines(ok), sp_step=step, engine=engine)
         want = LineBatch.from_lines([F.formulate_segments(s, sp_step=step, name=n) for n, s in ok])
         _same_batch(got, want)
     with pytest.raises(F.FormulationError, match="not dense enough"):
-        F.formulate_table(tab, sp_step=5.0)
+        F.formulate_table(tab, sp_step=5.0, engine=engine)
 
 
-def test_vectorised_discretiser_on_the_reference_goldens(formulation_golden, tmp_path):
+@pytest.mark.parametrize("engine", ["native", "numpy"])
+def test_vectorised_discretiser_on_the_reference_goldens(formulation_golden, tmp_path, engine):
     """The step-mode goldens produced by the reference's own Matrix_Formulation_Class, through the vectorised path."""
     g = formulation_golden
     csvs = split_blob(g["csv_blob"])
@@ -108,7 +110,7 @@ def test_vectorised_discretiser_on_the_reference_goldens(formulation_golden, tmp
         p.write_text(csvs[i])
         segs, _ = F.parse_line_csv(str(p))
         b = F.formulate_table(F.SegmentTable.from_lines([(str(name), segs)]), sp_step=float(g["param"][i]),
-                              technology=str(g["tech"]), temperature=float(g["temperature"]), givenWidth=float(g["width"]))
+                              technology=str(g["tech"]), temperature=float(g["temperature"]), givenWidth=float(g["width"]), engine=engine)
         t0, t1 = g["trip_off"][i], g["trip_off"][i + 1]
         u0, u1 = g["u_off"][i], g["u_off"][i + 1]
         assert int(b.num_nodes[0]) == int(g["num_nodes"][i]) and float(b.a_coeff[0]) == float(g["a_coeff"][i]), name
@@ -118,7 +120,8 @@ def test_vectorised_discretiser_on_the_reference_goldens(formulation_golden, tmp
     assert done >= 50
 
 
-def test_repeated_via_keys_and_one_point_segments():
+@pytest.mark.parametrize("engine", ["native", "numpy"])
+def test_repeated_via_keys_and_one_point_segments(engine):
     """Hand-made lines that hit the reference's dict overwrite (two joins at the same node) and the overwrite of the
     first / last entry of B by a via."""
     from proton_b200.api import LineBatch
@@ -130,7 +133,7 @@ def test_repeated_via_keys_and_one_point_segments():
     ]
     for step in (10.0, 1.0, 0.99):
         ok = [(n, s) for n, s in lines if min(x[2] for x in s) >= step]
-        got = F.formulate_table(F.SegmentTable.from_lines(ok), sp_step=step)
+        got = F.formulate_table(F.SegmentTable.from_lines(ok), sp_step=step, engine=engine)
         want = LineBatch.from_lines([F.formulate_segments(s, sp_step=step, name=n) for n, s in ok])
         _same_batch(got, want)
 
@@ -142,3 +145,35 @@ def test_workload_batches_equal_their_per_line_construction():
     a, b = W.ibmpg2_shaped_batch(replicas=3, seed=2), LineBatch.from_lines(W.ibmpg2_shaped_lines(replicas=3, seed=2))
     _same_batch(a, b)
     assert a.names == b.names
+
+
+def test_native_discretiser_equals_numpy_on_random_tables():
+    """proton_em_formulate_segments against the NumPy formulation on random segment tables built to hit the corners:
+    lengths at exact half-multiples of the step (round-half-to-even), one-point segments (vias on the first / last
+    node), runs of joins at one node (the dict overwrite), unnamed nodes, per-line steps."""
+    rng = np.random.default_rng(77)
+    for trial in range(40):
+        L = int(rng.integers(1, 60))
+        counts = rng.integers(1, 12, L)
+        K = int(counts.sum())
+        seg_off = np.zeros(L + 1, np.int64)
+        np.cumsum(counts, out=seg_off[1:])
+        step = np.repeat(rng.choice([0.5, 1.0, 2.0, 0.75], L), 1)
+        mult = rng.choice([1.0, 1.0, 1.5, 2.5, 3.0, 3.5, 1.0000001, 7.25, 40.0], K)
+        length = np.repeat(step, counts) * mult
+        tab = F.SegmentTable(names=[f"l{i}" for i in range(L)], seg_off=seg_off, length_um=length,
+                             current=rng.normal(0, 1e-3, K), lcoord=rng.integers(0, 3, (K, 2)).astype(np.int64),
+                             rcoord=rng.integers(0, 3, (K, 2)).astype(np.int64), named=rng.random(K) < 0.9)
+        for sp in (step, None if trial % 2 else float(step.min())):
+            try:
+                want = F.formulate_table(tab, sp_step=sp, engine="numpy")
+            except F.FormulationError as e:
+                with pytest.raises(F.FormulationError, match=str(e)[:20]):
+                    F.formulate_table(tab, sp_step=sp, engine="native")
+                continue
+            _same_batch(F.formulate_table(tab, sp_step=sp, engine="native"), want)
+    empty = F.SegmentTable(names=["x"], seg_off=np.array([0, 0]), length_um=np.zeros(0), current=np.zeros(0),
+                           lcoord=np.zeros((0, 2), np.int64), rcoord=np.zeros((0, 2), np.int64), named=np.zeros(0, bool))
+    for eng in ("native", "numpy"):
+        with pytest.raises(F.FormulationError, match="Corrupted"):
+            F.formulate_table(empty, engine=eng)
