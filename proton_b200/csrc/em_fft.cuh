@@ -401,6 +401,22 @@ __device__ __forceinline__ void fft_stage0_pruned(cplx* __restrict__ data, int g
   }
 }
 
+// Where the transformed chirp H of a row of NB * RADIX points keeps element q of the innermost butterfly b (logical,
+// digit-reversed index b * RADIX + q): at q * NB + b, so that the 16-byte loads of a warp — consecutive b, one q — are
+// contiguous (four 128-byte lines per request).  In butterfly order every lane sat in a line of its own: 32 lines per
+// request, and the H loads alone were 43 % of the L1 data-pipe wavefronts of the long row kernel
+// (profiles/r02_ncu_long_full.txt: 2.09 M of 4.9 M).
+#ifndef EM_HH_LANE_MAJOR
+#define EM_HH_LANE_MAJOR 1
+#endif
+template <int RADIX, int NB> __host__ __device__ constexpr int hh_pos(int b, int q) {
+  return EM_HH_LANE_MAJOR ? q * NB + b : b * RADIX + q;
+}
+// the same from the logical index i = b * RADIX + q of a row of `len` points
+__host__ __device__ constexpr int hh_pos_of(int len, int radix, int i) {
+  return EM_HH_LANE_MAJOR ? (i % radix) * (len / radix) + i / radix : i;
+}
+
 // Middle of Bluestein: last DIF stage (s = 1), product with H, first DIT stage (s = 1) in registers.
 template <int LOG2P, int RADIX, int NT>
 __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, const cplx* __restrict__ hhat, int tid) {
@@ -420,7 +436,7 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
         for (int q = 0; q < RADIX; ++q) v[q] = d[q];
         Dft<RADIX, -1>::run(v);
 #pragma unroll
-        for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], ldg_cplx(hhat + base + q));
+        for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], ldg_cplx(hhat + hh_pos<RADIX, NB>(b, q)));
         Dft<RADIX, +1>::run(v);
 #pragma unroll
         for (int q = 0; q < RADIX; ++q) d[q] = v[q];
@@ -429,7 +445,7 @@ __device__ __forceinline__ void fft_middle(cplx* __restrict__ data, int gcount, 
     }
     cplx h[RADIX];
 #pragma unroll
-    for (int q = 0; q < RADIX; ++q) h[q] = ldg_cplx(hhat + base + q);
+    for (int q = 0; q < RADIX; ++q) h[q] = ldg_cplx(hhat + hh_pos<RADIX, NB>(b, q));
     for (int g = g0; g < gcount; g += GSTEP) {
       cplx* d = data + g * TSTRIDE + pbase;
       cplx v[RADIX];

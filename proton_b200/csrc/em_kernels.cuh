@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(Cfg<LOG2P, BLUE>::NT) em_tables_kernel(const T
   }
   __syncthreads();
   DifStages<LOG2P, 0, plan_n(LOG2P), NT>::run(data, 1, twb, tid);
-  for (int i = tid; i < P; i += NT) hhat[i] = data[pad_idx<LOG2P>(i)];
+  for (int i = tid; i < P; i += NT) hhat[hh_pos_of(P, plan_radix(LOG2P, plan_n(LOG2P) - 1), i)] = data[pad_idx<LOG2P>(i)];
 }
 
 // Parameters of the short-line (dense) kernel.

@@ -422,7 +422,7 @@ __global__ void __launch_bounds__(kLongRowThreads, 2) em_long_row_kernel(const R
       fft_stage<LOG2P, stage_radix<LOG2P, NST - 1>(), 0, true, -1, NT, 0>(data, 1, twb, tid);
       __syncthreads();
       cplx* out = const_cast<cplx*>(p.tabs_build[s].hhat) + (long long)r * P2;
-      for (int i = tid; i < P2; i += NT) out[i] = data[pad_idx<LOG2P>(i)];
+      for (int i = tid; i < P2; i += NT) out[hh_pos_of(P2, stage_radix<LOG2P, NST - 1>(), i)] = data[pad_idx<LOG2P>(i)];
       return;
     }
     fft_middle<LOG2P, stage_radix<LOG2P, NST - 1>(), NT>(data, 1, hh, tid);

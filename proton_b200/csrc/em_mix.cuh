@@ -52,13 +52,13 @@ __device__ __forceinline__ void mix_middle(cplx* __restrict__ data, const cplx* 
     const int pbase = pad_idx<LR>(base);
     for (int g = g0; g < ODD; g += GSTEP) {
       cplx* d = data + g * RS + pbase;
-      const cplx* h = hhat + g * R + base;
+      const cplx* h = hhat + g * R;
       cplx v[RADIX];
 #pragma unroll
       for (int q = 0; q < RADIX; ++q) v[q] = d[q];
       Dft<RADIX, -1>::run(v);
 #pragma unroll
-      for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], ldg_cplx(h + q));
+      for (int q = 0; q < RADIX; ++q) v[q] = cmul(v[q], ldg_cplx(h + hh_pos<RADIX, NB>(b, q)));
       Dft<RADIX, +1>::run(v);
 #pragma unroll
       for (int q = 0; q < RADIX; ++q) d[q] = v[q];
@@ -251,7 +251,8 @@ __global__ void __launch_bounds__(MixCfg<LR, ODD>::NT) em_tables_mix_kernel(cons
   mix_colfwd<LR, ODD, NT, false>(data, twl, tid, 0);
   __syncthreads();
   DifStages<LR, 0, plan_n(LR), NT>::run(data, ODD, twb, tid);
-  for (int i = tid; i < P; i += NT) hhat[i] = data[(i >> LR) * RS + pad_idx<LR>(i & (R - 1))];
+  for (int i = tid; i < P; i += NT)
+    hhat[(i >> LR) * R + hh_pos_of(R, plan_radix(LR, plan_n(LR) - 1), i & (R - 1))] = data[(i >> LR) * RS + pad_idx<LR>(i & (R - 1))];
 }
 
 // w_P^{+j}, j < R, of a mixed length (one table per class, built at first use)

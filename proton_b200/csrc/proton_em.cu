@@ -1724,6 +1724,21 @@ int proton_em_debug_line_table(proton_em_plan* p, int64_t line, int which, doubl
     return PROTON_EM_OK;
   }
   CU_TRY(cudaMemcpy(out, src, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
+  if (which == 5) {
+    // H is kept lane-major per row (em_fft.cuh: hh_pos); hand it out in its logical order
+    const ClassOf c = classify(N);
+    const int lr = c.cls == CLS_BLUE ? c.log2p : c.cls == CLS_MIX ? mix_lr(c.log2p) : em::kLongLog2P2;
+    const long long R = 1LL << lr, rows = (n / 2) / R;
+    const int radix = em::plan_radix(lr, em::plan_n(lr) - 1);
+    std::vector<double> tmp((size_t)n);
+    std::memcpy(tmp.data(), out, (size_t)n * sizeof(double));
+    for (long long g = 0; g < rows; ++g)
+      for (long long i = 0; i < R; ++i) {
+        const long long at = g * R + em::hh_pos_of((int)R, radix, (int)i);
+        out[2 * (g * R + i)] = tmp[(size_t)(2 * at)];
+        out[2 * (g * R + i) + 1] = tmp[(size_t)(2 * at + 1)];
+      }
+  }
   return PROTON_EM_OK;
 }
 
