@@ -230,6 +230,11 @@ int proton_em_eval_line_noalloc(int device, void* stream, int32_t num_nodes, dou
                                 const double* d_ts, int32_t T, double critical_stress, double* d_stress,
                                 double* d_max_stress, int32_t* d_argmax, uint8_t* d_flag);
 
+/* Which kernel family evaluates a line of num_nodes nodes (host logic only, no GPU needed).  kind: 0 short-line DMMA
+ * kernel; 1 in-CTA FFT, N = 2^rows_log2; 2 in-CTA Bluestein, P = 2^rows_log2; 3 in-CTA Bluestein with `rows` rows of
+ * 2^rows_log2 points; 4 / 5 long path (power of two / Bluestein), `rows` rows of 4096 points; -1 longer than this build
+ * supports. */
+int proton_em_debug_class_of(int32_t num_nodes, int32_t* kind, int32_t* rows_log2, int32_t* rows);
 /* Test hook: y[i] = the device exp() used by the modal evaluation (must equal the host libm's). */
 int proton_em_debug_exp(proton_em_ctx* ctx, const double* x_host, double* y_host, int64_t n);
 /* Test hook: y[i] = exp(x[i]) - 1.0 exactly as the fused kernels evaluate the modal factor: bit-identical to the

@@ -105,7 +105,7 @@ int em_twin_dense(int N, double a, const double* lam, const double* W, const dou
 
 /* ---- stage plans: em_fft.cuh plan16 / plan_n / plan_radix / stage_tw_* / digit_pos ------------------------------- */
 static int lg2r(int r) { return r == 2 ? 1 : r == 4 ? 2 : r == 8 ? 3 : 4; }
-static int plan16(int p) { return p == 12 || p == 13; }
+static int plan16(int p) { return p == 8 || p == 12 || p == 13; }
 static int plan_n(int p) { return plan16(p) ? p / 4 + (p % 4 ? 1 : 0) : p / 3 + (p % 3 ? 1 : 0); }
 static int plan_radix(int p, int i) {
   return plan16(p) ? (i < p / 4 ? 16 : (p % 4 == 1 ? 2 : p % 4 == 2 ? 4 : 8)) : (i < p / 3 ? 8 : (p % 3 == 1 ? 2 : 4));

@@ -59,7 +59,8 @@ EXPORTS = ["proton_em_create", "proton_em_destroy", "proton_em_last_error", "pro
            "proton_em_eval_line_noalloc", "proton_em_debug_expm1", "proton_em_profile", "proton_em_profile_read",
            "proton_em_analyze_history_host", "proton_em_debug_line_table", "proton_em_pack_sigma0", "proton_em_run_cfgs",
            "proton_em_pack_from_project", "proton_em_plan_line_nodes", "proton_em_plan_set_line_names",
-           "proton_em_plan_line_name", "proton_em_formulate_segments"]
+           "proton_em_plan_line_name", "proton_em_formulate_segments",
+           "proton_em_debug_class_of"]
 
 
 def load() -> ctypes.CDLL:
@@ -106,6 +107,8 @@ def load() -> ctypes.CDLL:
         lib.proton_em_formulate_segments.argtypes = [ctypes.POINTER(Segments), vp, ctypes.c_double, ctypes.c_double,
                                                      ctypes.c_double, vp, vp, vp, vp, vp, vp, vp,
                                                      ctypes.POINTER(ctypes.c_int64)]
+    if hasattr(lib, "proton_em_debug_class_of"):
+        lib.proton_em_debug_class_of.argtypes = [ctypes.c_int32, c_i32p, c_i32p, c_i32p]
     lib.proton_em_debug_exp.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_debug_expm1.argtypes = [vp, vp, vp, ctypes.c_int64]
     lib.proton_em_eval_line_noalloc.argtypes = [ctypes.c_int, vp, ctypes.c_int32, ctypes.c_double, ctypes.c_int32, vp, vp,
@@ -125,3 +128,14 @@ def load() -> ctypes.CDLL:
 def check(rc: int) -> None:
     if rc != 0:
         raise ProtonEmError(rc, load().proton_em_last_error().decode(errors="replace"))
+
+
+KINDS = {0: "dense", 1: "fft_pow2", 2: "fft_blue", 3: "fft_mix", 4: "long_pow2", 5: "long_blue", -1: "none"}
+
+
+def class_of(n: int):
+    """(family, log2 of the row length, rows) of the kernel that evaluates a line of n nodes — the library's own
+    classify(), host logic only."""
+    k, lr, rows = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+    check(load().proton_em_debug_class_of(int(n), ctypes.byref(k), ctypes.byref(lr), ctypes.byref(rows)))
+    return KINDS[k.value], lr.value, rows.value

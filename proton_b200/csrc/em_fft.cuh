@@ -153,8 +153,14 @@ __host__ __device__ constexpr int lg2(int r) { return r == 2 ? 1 : r == 4 ? 2 : 
 #ifndef EM_RADIX16
 #define EM_RADIX16 1
 #endif
-// p = 12: 16 x 16 x 16;  p = 13: 16 x 16 x 16 x 2.
-__host__ __device__ constexpr bool plan16(int log2p) { return EM_RADIX16 != 0 && (log2p == 12 || log2p == 13); }
+// p = 8: 16 x 16 (the rows of the mixed-radix classes with up to 16 rows of 256 points, em_mix.cuh);  p = 12: 16 x 16 x 16;
+// p = 13: 16 x 16 x 16 x 2.
+#ifndef EM_PLAN16_8
+#define EM_PLAN16_8 1
+#endif
+__host__ __device__ constexpr bool plan16(int log2p) {
+  return EM_RADIX16 != 0 && ((EM_PLAN16_8 != 0 && log2p == 8) || log2p == 12 || log2p == 13);
+}
 __host__ __device__ constexpr int plan_n(int log2p) {
   return plan16(log2p) ? log2p / 4 + (log2p % 4 ? 1 : 0) : log2p / 3 + (log2p % 3 ? 1 : 0);
 }
@@ -216,7 +222,7 @@ template <int RADIX, int SIGN> __device__ __forceinline__ void twiddle_jit(cplx 
 // accesses and the digit-reversed scatter are free of bank conflicts for each of them.
 __host__ __device__ constexpr int pad_sh1(int log2p) { return plan_radix(log2p, plan_n(log2p) - 1) == 16 ? 4 : 3; }
 __host__ __device__ constexpr int pad_sh2(int log2p) {
-  return log2p == 6 ? 0 : (log2p == 7 || log2p == 8) ? 6 : log2p - lg2(plan_radix(log2p, 0));
+  return log2p == 6 ? 0 : log2p == 7 ? 6 : log2p == 8 ? (plan16(8) ? 0 : 6) : log2p - lg2(plan_radix(log2p, 0));
 }
 __host__ __device__ constexpr int pad_sh3(int log2p) { return (log2p == 13 && plan16(13)) ? 4 : 0; }
 __host__ __device__ constexpr int pad_idx_rt(int log2p, int p) {
@@ -254,7 +260,8 @@ template <int LOG2P, bool BLUE> struct Cfg {
 #ifndef EM_G10
 #define EM_G10 2
 #endif
-  static constexpr int NT = LOG2P >= 13 ? (plan16(13) ? 512 : 1024) : LOG2P == 12 ? (plan16(12) ? 256 : 512) : EM_NT_MID;
+  static constexpr int NT = LOG2P >= 13 ? (plan16(13) ? 512 : 1024) : LOG2P == 12 ? (plan16(12) ? 256 : 512)
+                            : (LOG2P == 8 && plan16(8)) ? 128 : EM_NT_MID;      // (p = 8: 16 butterflies x 8 transforms in flight)
   // rows of the staging buffer: N <= P (pow2) or N <= P/2 + 1 (Bluestein)
   static constexpr int NSTAGE = BLUE ? (P / 2 + 8) : P;
   static constexpr int G = LOG2P <= 6 ? 32 : LOG2P == 7 ? 16 : LOG2P == 8 ? 8 : LOG2P == 9 ? 4 : LOG2P == 10 ? EM_G10 : 1;
@@ -593,7 +600,7 @@ em_eval_fft_kernel(const EvalParams prm) {
         for (int b = (NB < NT ? tid % NB : tid); b < NB; b += BSTEP) {
           const int j = b;
           cplx w[8];
-          tw_powers<8>(twb[j], w);
+          if constexpr (R0 == 8) tw_powers<8>(twb[j], w);
           cplx post[QN];
           if (BLUE) {
 #pragma unroll
@@ -605,12 +612,16 @@ em_eval_fft_kernel(const EvalParams prm) {
           }
           for (int g = g0; g < gcount; g += GSTEP) {
             const cplx* d = data + g * TSTRIDE + pad_idx<LOG2P>(j);
-            cplx v[8];
+            cplx v[R0];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) v[q] = d[pad_off<LOG2P, LOG2P - 3>(q)];
+            for (int q = 0; q < R0; ++q) v[q] = d[pad_off<LOG2P, LOG2S0>(q)];
+            if constexpr (R0 == 8) {
 #pragma unroll
-            for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
-            Dft<8, +1>::run(v);
+              for (int q = 1; q < 8; ++q) v[q] = cmul(v[q], w[q]);
+            } else {
+              twiddle_jit<R0, +1>(v, twb[j]);
+            }
+            Dft<R0, +1>::run(v);
             double* s1 = stage + (size_t)g * 2 * C::NSTAGE;
             double* s2 = s1 + C::NSTAGE;
 #pragma unroll

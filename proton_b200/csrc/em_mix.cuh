@@ -1,4 +1,4 @@
-// em_mix.cuh — in-CTA Bluestein with mixed-radix lengths P = ODD x 2^LR (ODD = 5 or 6 rows of 2^LR points).
+// em_mix.cuh — in-CTA Bluestein with mixed-radix lengths P = ODD x 2^LR (ODD = 5 ... 16 rows of 2^LR points).
 //
 // em_eval_fft_kernel<p, true> pads every line to the next power of two P >= 2N-1, so a line just above a power of two
 // does twice the necessary transform length.  With the lengths 1.25 and 1.5 x 2^k in between, the average excess over
@@ -22,23 +22,26 @@
 
 namespace em {
 
-// Row counts: 5 (P = 1.25 x 2^k) and 6 (P = 1.5 x 2^k, as six half-length rows rather than three: an even row count
-// splits evenly over the row groups a CTA works on at a time, and 6 x 1024 points leave room for two CTAs per SM
-// where 3 x 2048 do not: measured 63 vs 42 Gevals/s at N = 3000).
+// Row counts.  5 and 6 rows (P = 1.25 and 1.5 x 2^k; six half-length rows rather than three: an even row count splits
+// evenly over the row groups a CTA works on at a time, measured 63 vs 42 Gevals/s at N = 3000) came first; the column
+// DFT handles any row count up to 16 in registers, so rows of 256 points give every multiple of 256 up to 4096 and rows
+// of 512 points every multiple of 512 up to 8192: the excess of P over 2N drops to a few per cent, and rows of 512
+// points need one stage less than the 1024-point rows the 5120- and 6144-point classes started with.
 template <int LR, int ODD> struct MixCfg {
   static constexpr int R = 1 << LR, P = ODD * R;
-  static constexpr int NT = LR >= 10 ? 256 : LR >= 8 ? 128 : 64;
-  // resident CTAs the register budget is sized for: 512 threads per SM for the long rows (128 registers; shared memory
-  // allows no more CTAs anyway), 768 for the short ones (80 registers: measured +3..13 % there, neutral for LR = 9)
-  static constexpr int MINB = (LR >= 9 ? 512 : 768) / NT;
+  static constexpr int NT = P > 6144 ? 512 : P > 3072 ? 256 : P >= 1024 ? 128 : 64;
+  // resident threads per SM the register budget is sized for: 512 (128 registers) where the rows run radix-16 stages,
+  // the column DFT holds nine or more values or the rows are long (shared memory allows no more CTAs there anyway),
+  // 768 (80 registers) for the short ones (measured +3..13 % there, neutral for LR = 9)
+  static constexpr int MINB = ((plan16(LR) || LR >= 9 || ODD >= 9) ? 512 : 768) / NT;
   static constexpr int RSTRIDE = padded_len<LR>();                    // padded row length (complex elements)
   static constexpr size_t tw_bytes = (size_t)stage_tw_total(LR) * sizeof(cplx);
   static constexpr size_t smem_bytes = tw_bytes + (size_t)ODD * RSTRIDE * sizeof(cplx);
   static constexpr int QN = (ODD + 1) / 2;                             // rows that can hold outputs m < N <= (P + 1) / 2
 };
 
-// code of a mixed class as the host keeps it in ClassOf::log2p / NTab::mix: (LR - 7) * 8 + ODD
-__host__ __device__ constexpr int mix_code(int lr, int odd) { return (lr - 7) * 8 + odd; }
+// code of a mixed class as the host keeps it in ClassOf::log2p / NTab::mix: (LR - 6) * 32 + ODD
+__host__ __device__ constexpr int mix_code(int lr, int odd) { return (lr - 6) * 32 + odd; }
 
 // Middle of Bluestein on ODD rows: last DIF stage, product with this row's slice of H, first DIT stage, in registers.
 template <int LR, int RADIX, int NT, int ODD>

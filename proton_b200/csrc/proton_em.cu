@@ -105,6 +105,33 @@ int small_max_n() {
   return v;
 }
 
+// The mixed-radix in-CTA classes that are built (rows of 2^lr points x odd rows, em_mix.cuh), each with its measured
+// cost: length of the longest line it takes / Gevals/s there (B200, T = 256, profiles/r02_class_rates.txt) — a time per
+// transform in arbitrary units.  A line goes to the admissible class (P >= 2N - 1) of least cost, power-of-two lengths
+// (kBlueCost) included.  Row counts that lost to the next longer class everywhere were taken out again:
+// 13 and 15 rows of 256 or 512 points (odd column DFTs cost O(rows^2) FP64 work; 14 x 256, 4096 and 7168, 8192 points
+// are cheaper).
+#define FOR_EACH_MIX(M)                                                                                               \
+  M(7, 5, 3.79) M(7, 6, 4.19) M(8, 5, 7.33) M(8, 6, 8.14) M(8, 7, 9.48) M(8, 9, 13.58) M(8, 11, 17.26)                 \
+  M(8, 14, 22.04) M(9, 5, 14.58) M(9, 6, 18.00) M(9, 9, 29.51) M(9, 10, 31.20) M(9, 11, 36.34) M(9, 12, 38.67)         \
+  M(9, 14, 49.46) M(9, 16, 52.63)
+struct MixClass { int lr, odd; double cost; };
+const MixClass kMixClasses[] = {
+#define M(lr, odd, cost) {lr, odd, cost},
+    FOR_EACH_MIX(M)
+#undef M
+};
+// the same for em_eval_fft_kernel<p, true>, P = 2^p (p <= 9 has no competitor: nominal)
+inline double blue_cost(int p) {
+  switch (p) {
+    case 10: return 5.63;
+    case 11: return 11.83;
+    case 12: return 22.52;
+    case 13: return 58.2;
+    default: return 0.0055 * (double)(1 << p);
+  }
+}
+
 ClassOf classify(int N) {
   if (N <= small_max_n() && !(N >= 64 && (N & (N - 1)) == 0)) return {CLS_SMALL, 0};
   if ((N & (N - 1)) == 0) {
@@ -131,24 +158,23 @@ ClassOf classify(int N) {
   }
   int p = 0;
   while ((1LL << p) < 2LL * N - 1) ++p;
-  // mixed-radix lengths 1.25 and 1.5 x 2^k (em_mix.cuh) when they are shorter than the power of two; PROTON_EM_MIX=0
-  // keeps the power-of-two lengths (for A/B runs)
+  // mixed-radix lengths (em_mix.cuh) when one is shorter than the power of two; PROTON_EM_MIX=0 keeps the
+  // power-of-two lengths (for A/B runs)
   static const bool use_mix = [] { const char* e = std::getenv("PROTON_EM_MIX"); return !(e && std::atoi(e) == 0); }();
   if (use_mix) {
     const long long need = 2LL * N - 1;
-    long long best = 1LL << p;
+    double best = blue_cost(p);
     int code = 0;
-    for (int lr = 7; lr <= 10; ++lr)
-      for (int odd : {5, 6}) {                                 // rows of 2^lr points
-        const long long P = (long long)odd << lr;
-        if (P >= need && P < best) { best = P; code = em::mix_code(lr, odd); }
-      }
+    for (const MixClass& m : kMixClasses) {
+      const long long P = (long long)m.odd << m.lr;
+      if (P >= need && m.cost < best) { best = m.cost; code = em::mix_code(m.lr, m.odd); }
+    }
     if (code) return {CLS_MIX, code};
   }
   return {CLS_BLUE, p};
 }
-inline int mix_lr(int code) { return code / 8 + 7; }
-inline int mix_odd(int code) { return code % 8; }
+inline int mix_lr(int code) { return code / 32 + 6; }
+inline int mix_odd(int code) { return code % 32; }
 
 // Bump allocator for the per-length tables (lives as long as the context).
 struct Arena {
@@ -242,7 +268,7 @@ struct proton_em_ctx {
   int64_t launches = 0;
   // long-line path: column twiddles per P1 and the wave scratch (grown on demand, reused by every call)
   em::cplx* d_twl[em::kLongMaxP1 + 1] = {};   // column twiddles per P1
-  em::cplx* d_twm[64] = {};                   // column twiddles per mixed class (em_mix.cuh), by mix_code
+  em::cplx* d_twm[192] = {};                   // column twiddles per mixed class (em_mix.cuh), by mix_code
   static constexpr int kLanes = 8;          // up to 8 streams; `lanes` of them are used (PROTON_EM_LANES, default 2:
                                             // two 32 MB waves in flight measured best, the scratch stays well inside L2)
   int lanes = 2;
@@ -394,10 +420,8 @@ int launch_eval_fft(proton_em_ctx* ctx, cudaStream_t st, bool blue, int log2p, c
   return PROTON_EM_OK;
 }
 
-#define FOR_EACH_MIX(M) M(7, 5) M(8, 5) M(9, 5) M(10, 5) M(7, 6) M(8, 6) M(9, 6) M(10, 6)
-
 int init_mix_attrs() {
-#define M(lr, odd)                                                                                                    \
+#define M(lr, odd, cost)                                                                                                    \
   CU_TRY(cudaFuncSetAttribute(em::em_eval_mix_kernel<lr, odd>, cudaFuncAttributeMaxDynamicSharedMemorySize,           \
                               (int)em::MixCfg<lr, odd>::smem_bytes));                                                 \
   CU_TRY(cudaFuncSetAttribute(em::em_tables_mix_kernel<lr, odd>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
@@ -423,7 +447,7 @@ int launch_tables_mix(proton_em_ctx* ctx, int code, const em::NTab* d_entries, i
   const int lr = mix_lr(code), odd = mix_odd(code);
   em::TableParams tp{d_entries, ctx->d_tw[lr]};
   bool done = false;
-#define M(l, o)                                                                                                       \
+#define M(l, o, c)                                                                                                      \
   if (lr == l && odd == o) {                                                                                          \
     em::em_tables_mix_kernel<l, o><<<count, em::MixCfg<l, o>::NT, em::MixCfg<l, o>::smem_bytes, ctx->stream>>>(tp, ctx->d_twm[code]); \
     done = true;                                                                                                      \
@@ -441,7 +465,7 @@ int launch_eval_mix(proton_em_ctx* ctx, cudaStream_t st, int code, const em::Eva
   const int lr = mix_lr(code), odd = mix_odd(code);
   em::MixParams mp{ep, ctx->d_twm[code]};
   bool done = false;
-#define M(l, o)                                                                                                       \
+#define M(l, o, c)                                                                                                      \
   if (lr == l && odd == o) {                                                                                          \
     em::em_eval_mix_kernel<l, o><<<grid, em::MixCfg<l, o>::NT, em::MixCfg<l, o>::smem_bytes, st>>>(mp);               \
     done = true;                                                                                                      \
@@ -707,7 +731,7 @@ int ensure_tables(proton_em_ctx* ctx, const std::vector<int>& distinct) {
   sorted.reserve(entries.size());
   struct Group { int blue, key; size_t off, cnt; bool is_long; bool is_mix = false; };
   std::vector<Group> groups;
-  for (int code = 1; code < 64; ++code) {
+  for (int code = 1; code < 192; ++code) {
     const size_t off = sorted.size();
     for (const em::NTab& t : entries)
       if (t.mix == code) sorted.push_back(t);
@@ -1078,12 +1102,12 @@ static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location,
       const int N = p->num_nodes[i];
       line_tab[i] = tab_index[N];
       const ClassOf c = classify(N);
-      lists[(int)c.cls * 64 + c.log2p].push_back((int)i);
+      lists[(int)c.cls * 256 + c.log2p].push_back((int)i);
     }
     for (auto& kv : lists) {
       proton_em_plan::ClassList cl;
-      cl.cls = (LineClass)(kv.first / 64);
-      cl.log2p = kv.first % 64;
+      cl.cls = (LineClass)(kv.first / 256);
+      cl.log2p = kv.first % 256;
       // longest lines first inside a class (they are the most expensive items)
       std::stable_sort(kv.second.begin(), kv.second.end(), [&](int x, int y) { return p->num_nodes[x] > p->num_nodes[y]; });
       cl.offset = (int)class_lines.size();
@@ -1738,6 +1762,22 @@ int proton_em_debug_line_table(proton_em_plan* p, int64_t line, int which, doubl
         out[2 * (g * R + i)] = tmp[(size_t)(2 * at)];
         out[2 * (g * R + i) + 1] = tmp[(size_t)(2 * at + 1)];
       }
+  }
+  return PROTON_EM_OK;
+}
+
+int proton_em_debug_class_of(int32_t num_nodes, int32_t* kind, int32_t* rows_log2, int32_t* rows) {
+  if (num_nodes < 1 || !kind || !rows_log2 || !rows) return fail(PROTON_EM_EINVAL, "proton_em_debug_class_of: bad arguments");
+  const ClassOf c = classify(num_nodes);
+  *rows_log2 = 0; *rows = 0;
+  switch (c.cls) {
+    case CLS_SMALL: *kind = 0; break;
+    case CLS_POW2: *kind = 1; *rows_log2 = c.log2p; *rows = 1; break;
+    case CLS_BLUE: *kind = 2; *rows_log2 = c.log2p; *rows = 1; break;
+    case CLS_MIX: *kind = 3; *rows_log2 = mix_lr(c.log2p); *rows = mix_odd(c.log2p); break;
+    case CLS_LPOW2: *kind = 4; *rows_log2 = em::kLongLog2P2; *rows = c.log2p; break;
+    case CLS_LBLUE: *kind = 5; *rows_log2 = em::kLongLog2P2; *rows = c.log2p; break;
+    default: *kind = -1; break;
   }
   return PROTON_EM_OK;
 }

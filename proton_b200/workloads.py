@@ -184,19 +184,10 @@ def config4_batch(target_nodes: int = 10_000_000, seed: int = 4) -> LineBatch:
     return base.subset(idx)
 
 
-def kernel_class(n: int, dense_max: int = 88) -> str:
-    """Which kernel family evaluates a line of n nodes (mirror of classify() in csrc/proton_em.cu)."""
-    pow2 = n & (n - 1) == 0
-    if n <= dense_max and not (pow2 and n >= 64):
-        return "dense"
-    if pow2:
-        return "fft_pow2" if n <= 8192 else "long_pow2"
-    if n > 4096:
-        return "long_blue"
-    need = 2 * n - 1
-    p2 = 1 << (need - 1).bit_length()
-    mixed = [rows << lr for lr in range(7, 11) for rows in (5, 6)]
-    return "fft_mix" if any(need <= P < p2 for P in mixed) else "fft_blue"
+def kernel_class(n: int) -> str:
+    """Which kernel family evaluates a line of n nodes (classify() of csrc/proton_em.cu, asked from the library)."""
+    from ._lib import class_of
+    return class_of(n)[0]
 
 
 def partition_lines(num_nodes: np.ndarray, world: int, T: int = 1) -> List[np.ndarray]:

@@ -11,7 +11,7 @@ def lg2(r):
 
 
 def plan(log2p):                      # em_fft.cuh: plan16 / plan_n / plan_radix
-    if log2p in (12, 13):
+    if log2p in (8, 12, 13):
         n = log2p // 4 + (1 if log2p % 4 else 0)
         return [16 if i < log2p // 4 else {1: 2, 2: 4, 3: 8}[log2p % 4] for i in range(n)]
     n = log2p // 3 + (1 if log2p % 3 else 0)
@@ -21,7 +21,7 @@ def plan(log2p):                      # em_fft.cuh: plan16 / plan_n / plan_radix
 def pad(log2p, p):                    # em_fft.cuh: pad_sh1 / pad_sh2 / pad_sh3 / pad_idx_rt
     pl = plan(log2p)
     sh1 = 4 if pl[-1] == 16 else 3
-    sh2 = 0 if log2p == 6 else 6 if log2p in (7, 8) else log2p - lg2(pl[0])
+    sh2 = 0 if log2p in (6, 8) else 6 if log2p == 7 else log2p - lg2(pl[0])
     sh3 = 4 if log2p == 13 else 0
     return p + (p >> sh1) + ((p >> sh2) if sh2 else 0) + ((p >> sh3) if sh3 else 0)
 
@@ -78,14 +78,18 @@ def padded_len(log2p):
     return (pad(log2p, (1 << log2p) - 1) + 8) & ~7
 
 
-@pytest.mark.parametrize("lr,rows", [(lr, rows) for lr in range(7, 11) for rows in (5, 6)])
+MIX_CLASSES = [(7, 5), (7, 6), (8, 5), (8, 6), (8, 7), (8, 9), (8, 11), (8, 14), (9, 5), (9, 6), (9, 9), (9, 10), (9, 11),
+               (9, 12), (9, 14), (9, 16)]                                   # FOR_EACH_MIX of csrc/proton_em.cu
+
+
+@pytest.mark.parametrize("lr,rows", MIX_CLASSES)
 def test_mixed_radix_rows_layout_and_choice(lr, rows):
     """em_mix.cuh: P = rows x 2^lr points as `rows` padded rows.  The column passes read and write element
     (row q, column j) for consecutive j per lane — conflict-free because a row's padding is conflict-free in natural order
-    and the row stride is a multiple of 8 elements — and the rows fit the shared memory the kernel asks for (two CTAs per
-    SM for the 5120- and 6144-point classes).  The host's choice of class (classify() in csrc/proton_em.cu, mirrored by
-    workloads.kernel_class) picks the shortest admissible length."""
-    from proton_b200.workloads import kernel_class
+    and the row stride is a multiple of 8 elements — and the rows fit the shared memory (two CTAs per SM for the 256-thread classes,
+    MixCfg).  The host's choice of class (classify() in
+    csrc/proton_em.cu) picks the admissible class of least measured cost."""
+    from proton_b200._lib import class_of
     R, rs = 1 << lr, padded_len(lr)
     assert rs % 8 == 0
     for q in range(rows):
@@ -93,12 +97,12 @@ def test_mixed_radix_rows_layout_and_choice(lr, rows):
     tw = sum((1 << (lr - sum(lg2(r) for r in plan(lr)[:i + 1]))) for i in range(len(plan(lr)))
              if lr - sum(lg2(r) for r in plan(lr)[:i + 1]) > 0)
     smem = (tw + rows * rs) * 16
-    assert smem <= 227 * 1024
-    if lr == 10:
-        assert 2 * (smem + 192 + 1024) <= 228 * 1024          # two CTAs per SM (1 KB per CTA is reserved by the runtime)
     P = rows << lr
+    nt = 512 if P > 6144 else 256 if P > 3072 else 128 if P >= 1024 else 64                  # MixCfg::NT / MINB
+    minb = (512 if (lr >= 8 or rows >= 9) else 768) // nt
+    assert smem + 192 <= 227 * 1024
+    if 3072 < P <= 6144:                                       # 256 threads, 128 registers: two CTAs per SM must fit
+        assert nt == 256 and minb == 2 and 2 * (smem + 192 + 1024) <= 228 * 1024, (smem, minb)   # (1 KB per CTA is reserved)
     n_max = (P + 1) // 2                                       # 2N - 1 <= P
-    assert kernel_class(n_max) == "fft_mix"
-    lengths = sorted({r << l for l in range(7, 11) for r in (5, 6)} | {1 << p for p in range(7, 14)})
-    prev = max(x for x in lengths if x < P)
-    assert kernel_class((prev + 1) // 2 + 1) == "fft_mix"       # just above the next shorter length: this class
+    n = n_max - 1 if n_max & (n_max - 1) == 0 else n_max       # (a power-of-two line has its own kernel)
+    assert class_of(n) == ("fft_mix", lr, rows)                # cheapest admissible class for the longest line it takes

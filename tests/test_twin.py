@@ -47,21 +47,23 @@ def test_gpu_field_and_reductions_equal_the_cpu_twin_bit_for_bit(oracle, kind, s
 
 
 def _class_of(n):
-    """(kind, lr, rows) of a non-power-of-two line above the dense limit — mirror of classify() in csrc/proton_em.cu."""
-    need = 2 * n - 1
-    if n > 4096:
-        return None                      # long path: the row count comes from the device table (see below)
-    p2 = 1 << (need - 1).bit_length()
-    best = min(((r << lr), lr, r) for lr in range(7, 11) for r in (5, 6) if (r << lr) >= need) if need <= (6 << 10) else None
-    if best and best[0] < p2:
-        return ("mix", best[1], best[2])
-    return ("blue", 0, 0)
+    """(kind, lr, rows) of a non-power-of-two line above the dense limit, from the library's own classify()."""
+    from proton_b200._lib import class_of
+    kind, lr, rows = class_of(n)
+    assert kind in ("fft_blue", "fft_mix"), (n, kind)
+    return ("mix", lr, rows) if kind == "fft_mix" else ("blue", 0, 0)
 
 
-@pytest.mark.parametrize("sizes", [[100, 129, 200, 255, 400, 511, 777, 1000, 2047, 3500, 4095],          # P = 2^p
-                                   [257, 300, 330, 360, 513, 600, 700, 1025, 1100, 1300, 1500, 2049, 2500, 2600, 3000]])
+# one length just below the capacity of every mixed class (rows x 2^lr >= 2N - 1), plus lengths that stay on 2^p
+MIX_CLASSES = [(7, 5), (7, 6), (8, 5), (8, 6), (8, 7), (8, 9), (8, 11), (8, 14), (9, 5), (9, 6), (9, 9), (9, 10), (9, 11),
+               (9, 12), (9, 14), (9, 16)]
+MIX_SIZES = [(rows << lr) // 2 - 3 for lr, rows in MIX_CLASSES]
+
+
+@pytest.mark.parametrize("sizes", [[100, 129, 200, 255, 400, 511, 1000, 2047],                # P = 2^p
+                                   [300, 330, 360, 600, 700, 1100, 1300, 1500, 2500, 3000], MIX_SIZES])
 def test_bluestein_classes_equal_the_cpu_twin_bit_for_bit(oracle, sizes):
-    """In-CTA Bluestein with power-of-two and with mixed-radix lengths (5 or 6 rows of 2^k points)."""
+    """In-CTA Bluestein with power-of-two and with mixed-radix lengths (5 to 16 rows of 2^k points)."""
     from proton_b200.api import Context
     rng = np.random.default_rng(8)
     batch = synth_batch(rng, sizes)
@@ -82,7 +84,9 @@ def test_bluestein_classes_equal_the_cpu_twin_bit_for_bit(oracle, sizes):
             assert same.all(), (f"N={n} {kind} lr={lr} rows={rows}: {np.count_nonzero(~same)} of {same.size} values differ, "
                                 f"worst {np.abs(g - want).max() / np.abs(want).max():.3e}")
             assert np.array_equal(got.max_stress[l], want.max(axis=1)) and np.array_equal(got.argmax[l], want.argmax(axis=1))
-        assert len(kinds) == 1 or len(kinds) >= 6          # the second list goes through six mixed-radix classes
+        assert len(kinds) == 1 or len(kinds) >= 6          # the other lists go through the mixed-radix classes
+        if sizes is MIX_SIZES:
+            assert len(kinds) == len(MIX_SIZES), kinds
         plan.close()
     finally:
         ctx.close()
