@@ -1,17 +1,16 @@
 // em_mix.cuh — in-CTA Bluestein with mixed-radix lengths P = ODD x 2^LR (ODD = 5 ... 16 rows of 2^LR points).
 //
 // em_eval_fft_kernel<p, true> pads every line to the next power of two P >= 2N-1, so a line just above a power of two
-// does twice the necessary transform length.  With the lengths 1.25 and 1.5 x 2^k in between, the average excess over
-// 2N drops from 44 % to 17 % for line lengths spread evenly in log N, and lines of 2049..3072 nodes need 5120 or 6144
-// points instead of 8192 — two CTAs per SM instead of one.  Measured on B200 (T = 256): +24..47 % on the lengths that
-// change class, synthetic ragged batch 66.0 -> 57.7 ms per step.
+// does twice the necessary transform length.  With 5 and 6 rows (1.25 and 1.5 x 2^k) in between, the average excess over
+// 2N dropped from 44 % to 20 % for line lengths spread evenly in log N (synthetic ragged batch 66.0 -> 57.7 ms per step on
+// B200, T = 256); with every row count up to 16 that pays (rows of 256 and 512 points) it is 9 % (52.3 -> 49.2 ms).
 //
 // Structure: the long path's three passes (em_long.cuh) inside one CTA, with shared memory in place of the L2 scratch.
 // The P points are ODD rows of R = 2^LR points, element index i = j + q R (row q, column j):
 //   modal phase   chirped, packed spectrum a_k written at (row k / R, column k % R)               [em_fft.cuh phase 1]
 //   column pass   y_r[j] = (sum_q x[j + q R] w_ODD^{-q r}) w_P^{-j r}     (inputs with j + q R >= N are zero)
 //   row pass      R-point DIF on the ODD rows at once (the rows play the part of em_fft.cuh's transforms in flight),
-//                 last DIF stage x H x first DIT stage in registers (H stored row by row, digit-reversed inside a row),
+//                 last DIF stage x H x first DIT stage in registers (H stored row by row, lane-major inside a row: hh_pos),
 //                 DIT back down to stage 0
 //   column pass   u[j + q R] = sum_r (X_r[j] w_P^{+j r}) w_ODD^{+q r}, post-chirp, de-interleave (Makhoul's permutation),
 //                 stress store straight to global memory, max / argmax / flag per (line, timestamp)

@@ -4,12 +4,14 @@
 // resident in HBM) and the launch logic that routes each line to a kernel by its length:
 //   N <= 88 (not 64)             em_eval_dense_kernel<MT>       (DMMA contraction with the N x N cosine matrix)
 //   N = 2^p, 64..8192            em_eval_fft_kernel<p, false>   (in-CTA DIT FFT, radix 16/8/4/2)
-//   other N <= 4096              em_eval_fft_kernel<p, true>    (Bluestein, P = 2^p >= 2N-1), or
-//                                em_eval_mix_kernel<LR, ROWS>   (Bluestein, P = 5 or 6 x 2^LR when that is shorter)
+//   other N <= 4096              em_eval_fft_kernel<p, true>    (Bluestein, P = 2^p >= 2N-1, P <= 4096), or
+//                                em_eval_mix_kernel<LR, ROWS>   (Bluestein, P = ROWS x 2^LR, 5..16 rows of 128 / 256 / 512
+//                                                                points: the admissible class of least measured cost)
 //   other N <= 65536, 2^p <= 131072   em_long_{colfwd_paired | scatter} -> em_long_row -> em_long_colinv
 //                                (P = P1 x 4096 through an L2-resident scratch, waves dealt to `lanes` streams)
 // Tuning knobs, all optional environment variables read once: PROTON_EM_LANES (2), PROTON_EM_LONG_WAVE_MB (32),
-// PROTON_EM_PDL (1), PROTON_EM_COL_DIV (48), PROTON_EM_DENSE_MAX (88), PROTON_EM_CHUNK_MB (256), PROTON_EM_TRACE.
+// PROTON_EM_PDL (1), PROTON_EM_COL_DIV (48), PROTON_EM_DENSE_MAX (88), PROTON_EM_CHUNK_MB (256), PROTON_EM_MIX (1),
+// PROTON_EM_TRACE.
 // There is no CPU fallback: every entry point fails with PROTON_EM_ECUDA when no device is usable.
 #include "../../include/proton_em.h"
 
