@@ -106,3 +106,29 @@ def test_mixed_radix_rows_layout_and_choice(lr, rows):
     n_max = (P + 1) // 2                                       # 2N - 1 <= P
     n = n_max - 1 if n_max & (n_max - 1) == 0 else n_max       # (a power-of-two line has its own kernel)
     assert class_of(n) == ("fft_mix", lr, rows)                # cheapest admissible class for the longest line it takes
+
+
+def test_every_line_length_gets_an_admissible_transform():
+    """classify() (through proton_em_debug_class_of) for every line length the build supports: the transform of the
+    chosen class is long enough for Bluestein (P >= 2N - 1), never longer than the next power of two, and the class
+    is one that is built."""
+    from proton_b200._lib import class_of
+    built = set(MIX_CLASSES)
+    for n in list(range(1, 4200)) + list(range(4200, 65537, 37)) + [65535, 65536, 131072]:
+        kind, lr, rows = class_of(n)
+        pow2 = n & (n - 1) == 0
+        need = 2 * n - 1
+        if kind == "dense":
+            assert n <= 88 and not (pow2 and n >= 64)
+        elif kind == "fft_pow2":
+            assert pow2 and 64 <= n <= 8192 and (1 << lr) == n
+        elif kind == "fft_blue":
+            assert not pow2 and (1 << lr) >= need and (1 << (lr - 1)) < need and lr <= 12
+        elif kind == "fft_mix":
+            P = rows << lr
+            assert (lr, rows) in built and need <= P <= 1 << (need - 1).bit_length() and n <= 4096
+        elif kind == "long_pow2":
+            assert pow2 and n > 8192 and rows * 4096 == n
+        else:
+            assert kind == "long_blue" and 4096 < n <= 65536 and rows * 4096 >= need and rows <= 32
+    assert class_of(65537)[0] == "none" and class_of(262144)[0] == "none"
