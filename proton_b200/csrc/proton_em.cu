@@ -10,7 +10,7 @@
 //   other N <= 65536, 2^p <= 131072   em_long_{colfwd_paired | scatter} -> em_long_row -> em_long_colinv
 //                                (P = P1 x 4096 through an L2-resident scratch, waves dealt to `lanes` streams)
 // Tuning knobs, all optional environment variables read once: PROTON_EM_LANES (2), PROTON_EM_LONG_WAVE_MB (32),
-// PROTON_EM_PDL (1), PROTON_EM_COL_DIV (48), PROTON_EM_DENSE_MAX (88), PROTON_EM_CHUNK_MB (256), PROTON_EM_MIX (1),
+// PROTON_EM_PDL (1), PROTON_EM_COL_DIV (32), PROTON_EM_DENSE_MAX (88), PROTON_EM_CHUNK_MB (256), PROTON_EM_MIX (1),
 // PROTON_EM_TRACE.
 // There is no CPU fallback: every entry point fails with PROTON_EM_ECUDA when no device is usable.
 #include "../../include/proton_em.h"
@@ -1314,7 +1314,7 @@ static int eval_long_all(proton_em_plan* p, const std::vector<const proton_em_pl
       w.part_v = ctx->long_part_v.p; w.part_i = ctx->long_part_i.p;
       w.mx = d_mx; w.amx = d_amx; w.flag = d_flag;
       w.critical = critical;
-      static const int col_div = [] { const char* e = std::getenv("PROTON_EM_COL_DIV"); const int v = e ? std::atoi(e) : 0; return v > 0 ? v : 48; }();
+      static const int col_div = [] { const char* e = std::getenv("PROTON_EM_COL_DIV"); const int v = e ? std::atoi(e) : 0; return v > 0 ? v : 32; }();
       const int tpc = std::max(1, cnt / col_div);
       const int groups = (cnt + tpc - 1) / tpc;
       em::ColParams cp{w, 0, nullptr, tpc, ctx->d_twl[lp1]};
