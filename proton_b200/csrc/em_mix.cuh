@@ -2,8 +2,9 @@
 //
 // em_eval_fft_kernel<p, true> pads every line to the next power of two P >= 2N-1, so a line just above a power of two
 // does twice the necessary transform length.  With 5 and 6 rows (1.25 and 1.5 x 2^k) in between, the average excess over
-// 2N dropped from 44 % to 20 % for line lengths spread evenly in log N (synthetic ragged batch 66.0 -> 57.7 ms per step on
-// B200, T = 256); with every row count up to 16 that pays (rows of 256 and 512 points) it is 9 % (52.3 -> 49.2 ms).
+// 2N dropped from 44 % to 19 % for line lengths spread evenly in log N (synthetic ragged batch 66.0 -> 57.7 ms per step on
+// B200, T = 256); with every row count up to 16 that pays (rows of 256 and 512 points) it is 16 % overall and 7 % from
+// 640 nodes up (52.3 -> 49.2 ms).
 //
 // Structure: the long path's three passes (em_long.cuh) inside one CTA, with shared memory in place of the L2 scratch.
 // The P points are ODD rows of R = 2^LR points, element index i = j + q R (row q, column j):
