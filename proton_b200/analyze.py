@@ -108,15 +108,22 @@ def formulate_for_analyze(csv_files: Sequence[str], technology: str, temperature
 
 
 def write_reference_outputs(project_dir: str, names, result, timestamps, technology, temperature, width) -> int:
-    """stress_<%f>.txt per (line, t) exactly where and how the reference binary writes them."""
+    """stress_<%f>.txt per (line, t) exactly where and how the reference binary writes them; returns the number of files.
+    The file name carries `std::to_string(t)`, i.e. six decimals (bin/EMtool_analytical@0xbca3): timestamps that print
+    the same way share one file, and the reference — one process per (line, t), run one after the other — leaves the
+    LAST of them in it (the readers match `stress_([\\d.]+)\\.` and compare floats,
+    PROTON_cli.py:1039-1048).  Same here: only the last timestamp of each file name is written."""
+    ts = [float(t) for t in timestamps]
+    fname = ["stress_" + ("%f" % t) + ".txt" for t in ts]
+    last = {f: j for j, f in enumerate(fname)}             # a later timestamp with the same name wins
     n = 0
     for l, name in enumerate(names):
         out_dir = os.path.join(project_dir, "output", name, f"{technology}_{temperature}_{width}")
         os.makedirs(out_dir, exist_ok=True)
         block = result.line(l)
-        for j, t in enumerate(timestamps):
-            with open(os.path.join(out_dir, "stress_" + ("%f" % float(t)) + ".txt"), "w") as f:
-                f.write("".join("%.18g\n" % v for v in block[j]))
+        for f, j in last.items():
+            with open(os.path.join(out_dir, f), "w") as fh:
+                fh.write("".join("%.18g\n" % v for v in block[j]))
             n += 1
     return n
 
