@@ -28,6 +28,7 @@
 #include <string>
 #include <thread>
 #include <map>
+#include <new>
 #include <unordered_map>
 #include <vector>
 #include <sys/stat.h>
@@ -63,6 +64,12 @@ int fail(int code, const char* fmt, ...) {
   g_last_error = buf;
   return code;
 }
+
+// No exception leaves the C ABI (include/proton_em.h: "nothing here throws"): the entry points that build host-side
+// containers are function-try-blocks that end in this.
+#define EM_ABI_CATCH(name)                                                                          \
+  catch (const std::bad_alloc&) { return fail(PROTON_EM_ENOMEM, name ": out of host memory"); }    \
+  catch (const std::exception& e) { return fail(PROTON_EM_EINVAL, name ": %s", e.what()); }
 
 #define CU_TRY(expr)                                                                              \
   do {                                                                                            \
@@ -813,7 +820,7 @@ extern "C" {
 const char* proton_em_last_error(void) { return g_last_error.c_str(); }
 const char* proton_em_version(void) { return "proton_em 0.1 (sm_100a)"; }
 
-int proton_em_create(proton_em_ctx** out, int device) {
+int proton_em_create(proton_em_ctx** out, int device) try {
   if (!out) return fail(PROTON_EM_EINVAL, "proton_em_create: out is NULL");
   *out = nullptr;
   int ndev = 0;
@@ -907,7 +914,7 @@ int proton_em_create(proton_em_ctx** out, int device) {
   if (rc) { proton_em_destroy(ctx); return rc; }
   *out = ctx;
   return PROTON_EM_OK;
-}
+} EM_ABI_CATCH("proton_em_create")
 
 int proton_em_destroy(proton_em_ctx* ctx) {
   if (!ctx) return PROTON_EM_OK;
@@ -988,14 +995,14 @@ int64_t proton_em_plan_num_lines(const proton_em_plan* plan) { return plan ? pla
 int32_t proton_em_plan_line_nodes(const proton_em_plan* plan, int64_t line) {
   return (plan && line >= 0 && line < plan->L) ? plan->num_nodes[(size_t)line] : 0;
 }
-int proton_em_plan_set_line_names(proton_em_plan* plan, const char* const* names, int64_t n) {
+int proton_em_plan_set_line_names(proton_em_plan* plan, const char* const* names, int64_t n) try {
   if (!plan) return fail(PROTON_EM_EINVAL, "proton_em_plan_set_line_names: null plan");
   if (n != plan->L || (n > 0 && !names)) return fail(PROTON_EM_EINVAL, "proton_em_plan_set_line_names: the plan has %lld lines, %lld names given", (long long)plan->L, (long long)n);
   std::vector<std::string> v((size_t)n);
   for (int64_t i = 0; i < n; ++i) v[(size_t)i] = names[i] ? names[i] : "";
   plan->names.swap(v);
   return PROTON_EM_OK;
-}
+} EM_ABI_CATCH("proton_em_plan_set_line_names")
 const char* proton_em_plan_line_name(const proton_em_plan* plan, int64_t line) {
   if (!plan || line < 0 || (size_t)line >= plan->names.size()) return nullptr;
   return plan->names[(size_t)line].c_str();
@@ -1009,15 +1016,15 @@ int64_t proton_em_plan_scratch_bytes(const proton_em_plan* p) {
 static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out,
                      const double* sigma0 = nullptr);
 
-int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, proton_em_plan** out) {
+int proton_em_pack(proton_em_ctx* ctx, const proton_em_batch* b, int location, proton_em_plan** out) try {
   return pack_impl(ctx, b, location, 0, out);
-}
+} EM_ABI_CATCH("proton_em_pack")
 
 int proton_em_pack_sigma0(proton_em_ctx* ctx, const proton_em_batch* b, const double* sigma0, int location,
-                          proton_em_plan** out) {
+                          proton_em_plan** out) try {
   if (!sigma0 && b && b->num_lines > 0) return fail(PROTON_EM_EINVAL, "proton_em_pack_sigma0: sigma0 is NULL");
   return pack_impl(ctx, b, location, 0, out, sigma0);
-}
+} EM_ABI_CATCH("proton_em_pack_sigma0")
 
 static int pack_impl(proton_em_ctx* ctx, const proton_em_batch* b, int location, int64_t chunk_nodes, proton_em_plan** out,
                      const double* sigma0) {
@@ -1503,7 +1510,7 @@ static int eval_device_core(proton_em_plan* p, const double* d_ts, int T, const 
 }
 
 int proton_em_eval(proton_em_plan* p, const double* ts, int32_t T, const proton_em_opts* opts,
-                   const proton_em_result* res, int location) {
+                   const proton_em_result* res, int location) try {
   if (!p || !res) return fail(PROTON_EM_EINVAL, "proton_em_eval: NULL argument");
   if (T < 0) return fail(PROTON_EM_EINVAL, "T < 0");
   if (T == 0 || p->L == 0) return PROTON_EM_OK;
@@ -1532,10 +1539,10 @@ int proton_em_eval(proton_em_plan* p, const double* ts, int32_t T, const proton_
   CU_TRY(cudaMemcpyAsync(res->flag, d_flag.p, d_flag.bytes(), cudaMemcpyDeviceToHost, ctx->stream));
   CU_TRY(cudaStreamSynchronize(ctx->stream));
   return PROTON_EM_OK;
-}
+} EM_ABI_CATCH("proton_em_eval")
 
 int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const double* ts, int32_t T,
-                           const proton_em_opts* opts, const proton_em_result* res, int64_t max_device_bytes) {
+                           const proton_em_opts* opts, const proton_em_result* res, int64_t max_device_bytes) try {
   if (!ctx || !b || !res) return fail(PROTON_EM_EINVAL, "proton_em_analyze_host: NULL argument");
   if (T <= 0 || b->num_lines <= 0) return PROTON_EM_OK;
   if (!ts || !res->max_stress || !res->argmax || !res->flag)
@@ -1595,11 +1602,11 @@ int proton_em_analyze_host(proton_em_ctx* ctx, const proton_em_batch* b, const d
   CU_TRY(cudaStreamSynchronize(cs));
   tr.lap("copy stream done");
   return PROTON_EM_OK;
-}
+} EM_ABI_CATCH("proton_em_analyze_host")
 
 int proton_em_analyze_history_host(proton_em_ctx* ctx, const proton_em_batch* b, const double* const* curden_seg,
                                    const double* seg_start, int32_t num_segments, const double* ts, int32_t T,
-                                   const proton_em_opts* opts, const proton_em_result* res) {
+                                   const proton_em_opts* opts, const proton_em_result* res) try {
   if (!ctx || !b || !res || !curden_seg || !seg_start)
     return fail(PROTON_EM_EINVAL, "proton_em_analyze_history_host: NULL argument");
   if (num_segments <= 0) return fail(PROTON_EM_EINVAL, "proton_em_analyze_history_host: need at least one segment");
@@ -1698,11 +1705,11 @@ int proton_em_analyze_history_host(proton_em_ctx* ctx, const proton_em_batch* b,
   CU_TRY(cudaStreamSynchronize(st));
   CU_TRY(cudaStreamSynchronize(cs));
   return PROTON_EM_OK;
-}
+} EM_ABI_CATCH("proton_em_analyze_history_host")
 
 static int debug_exp_impl(proton_em_ctx* ctx, const double* x, double* y, int64_t n, int which);
 
-int proton_em_debug_line_table(proton_em_plan* p, int64_t line, int which, double* out, int64_t capacity, int64_t* count) {
+int proton_em_debug_line_table(proton_em_plan* p, int64_t line, int which, double* out, int64_t capacity, int64_t* count) try {
   if (!p || !out || !count) return fail(PROTON_EM_EINVAL, "proton_em_debug_line_table: NULL argument");
   if (line < 0 || line >= p->L) return fail(PROTON_EM_EINVAL, "line %lld out of range", (long long)line);
   proton_em_ctx* ctx = p->ctx;
@@ -1766,7 +1773,7 @@ int proton_em_debug_line_table(proton_em_plan* p, int64_t line, int which, doubl
       }
   }
   return PROTON_EM_OK;
-}
+} EM_ABI_CATCH("proton_em_debug_line_table")
 
 int proton_em_debug_class_of(int32_t num_nodes, int32_t* kind, int32_t* rows_log2, int32_t* rows) {
   if (num_nodes < 1 || !kind || !rows_log2 || !rows) return fail(PROTON_EM_EINVAL, "proton_em_debug_class_of: bad arguments");

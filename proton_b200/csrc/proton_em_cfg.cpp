@@ -21,6 +21,7 @@
 #include <cstring>
 #include <dirent.h>
 #include <fstream>
+#include <new>
 #include <sstream>
 #include <string>
 #include <sys/stat.h>
@@ -177,7 +178,12 @@ int write_stress_file(const CfgLine& ln, const double* stress, std::string& text
 
 }  // namespace
 
-extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_t msg_len) {
+// No exception leaves the C ABI: the entry points below are function-try-blocks that end in this.
+#define EM_CFG_CATCH                                                                                                  \
+  catch (const std::bad_alloc&) { set_msg(msg, msg_len, "Out of host memory.\n"); return PROTON_EM_ENOMEM; }          \
+  catch (const std::exception& e) { set_msg(msg, msg_len, std::string(e.what()) + "\n"); return PROTON_EM_EINVAL; }
+
+extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char* msg, size_t msg_len) try {
   set_msg(msg, msg_len, "");
   CfgLine ln;
   std::string text;
@@ -196,7 +202,7 @@ extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char*
   const int wrc = write_stress_file(ln, stress.data(), text);
   if (wrc) set_msg(msg, msg_len, text);
   return wrc;
-}
+} EM_CFG_CATCH
 
 // Many analytical.cfg files in one call — what PROTON_cli.analyze starts as one process per line
 // (PROTON_cli.py:1174-1181).  Every cfg is read like proton_em_run_cfg reads it; the lines that read cleanly form ONE
@@ -205,7 +211,7 @@ extern "C" int proton_em_run_cfg(proton_em_ctx* ctx, const char* cfg_path, char*
 // cfgs that failed, or a negative PROTON_EM_E* code if the batched evaluation itself failed (message in `msg`, which
 // otherwise holds the reference's stdout text of the first failing cfg).
 extern "C" int proton_em_run_cfgs(proton_em_ctx* ctx, const char* const* cfg_paths, int64_t n, int32_t* status,
-                                  char* msg, size_t msg_len) {
+                                  char* msg, size_t msg_len) try {
   set_msg(msg, msg_len, "");
   if (n < 0 || (n > 0 && !cfg_paths)) { set_msg(msg, msg_len, "proton_em_run_cfgs: bad arguments.\n"); return PROTON_EM_EINVAL; }
   if (!ctx) { set_msg(msg, msg_len, "No CUDA context.\n"); return PROTON_EM_ECUDA; }
@@ -266,7 +272,7 @@ extern "C" int proton_em_run_cfgs(proton_em_ctx* ctx, const char* const* cfg_pat
     }
   }
   return failed;
-}
+} EM_CFG_CATCH
 
 // ---------------------------------------------------------------------------------------------------------------------
 // proton_em_pack_from_project: every discretised line of a PROTON project directory in one plan.
@@ -324,7 +330,7 @@ int read_analytical_txt(const std::string& path, CfgLine& out) {
 }  // namespace
 
 extern "C" int proton_em_pack_from_project(proton_em_ctx* ctx, const char* project_dir, const char* variant,
-                                           proton_em_plan** out, int64_t* skipped, char* msg, size_t msg_len) {
+                                           proton_em_plan** out, int64_t* skipped, char* msg, size_t msg_len) try {
   set_msg(msg, msg_len, "");
   if (skipped) *skipped = 0;
   if (!out || !project_dir) { set_msg(msg, msg_len, "proton_em_pack_from_project: bad arguments.\n"); return PROTON_EM_EINVAL; }
@@ -395,4 +401,4 @@ extern "C" int proton_em_pack_from_project(proton_em_ctx* ctx, const char* proje
   const int prc = proton_em_pack(ctx, &batch, PROTON_EM_HOST, out);
   if (prc != PROTON_EM_OK) { set_msg(msg, msg_len, std::string(proton_em_last_error()) + "\n"); return prc; }
   return proton_em_plan_set_line_names(*out, names.data(), (int64_t)names.size());
-}
+} EM_CFG_CATCH
