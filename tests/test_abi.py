@@ -42,3 +42,30 @@ def test_product_never_imports_the_oracle():
         if p.suffix in (".py", ".cu", ".cuh", ".cpp", ".h"):
             txt = p.read_text()
             assert "oracle" not in txt.replace("no oracle", ""), f"{p} mentions the oracle"
+
+
+def test_host_only_entry_points_and_argument_checks_need_no_gpu(tmp_path):
+    """The parts of the ABI that are host logic answer without a device: the class of a line length, the discretiser,
+    plan accessors on NULL, and the file-level entry points' argument checks (no context -> PROTON_EM_ECUDA with the
+    message in `msg`, nothing read or written)."""
+    lib = ctypes.CDLL(str(_built()))
+    k, lr, rows = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+    assert lib.proton_em_debug_class_of(19087, ctypes.byref(k), ctypes.byref(lr), ctypes.byref(rows)) == 0
+    assert (k.value, lr.value, rows.value) == (5, 12, 10)                  # long Bluestein path, 10 rows of 4096 points
+    assert lib.proton_em_debug_class_of(0, ctypes.byref(k), ctypes.byref(lr), ctypes.byref(rows)) == -1
+    lib.proton_em_plan_line_name.restype = ctypes.c_char_p
+    assert lib.proton_em_plan_line_name(None, ctypes.c_int64(0)) is None
+    lib.proton_em_plan_num_lines.restype = ctypes.c_int64
+    assert lib.proton_em_plan_num_lines(None) == 0 and lib.proton_em_plan_line_nodes(None, ctypes.c_int64(0)) == 0
+    assert lib.proton_em_formulate_segments(None, None, ctypes.c_double(1.0), ctypes.c_double(1.0), ctypes.c_double(1.0),
+                                            None, None, None, None, None, None, None, None) == -1
+    msg = ctypes.create_string_buffer(256)
+    plan, skipped = ctypes.c_void_p(), ctypes.c_int64(7)
+    (tmp_path / "input" / "M1_x" / "CuDD_378.0_0.1").mkdir(parents=True)
+    rc = lib.proton_em_pack_from_project(None, str(tmp_path).encode(), None, ctypes.byref(plan), ctypes.byref(skipped),
+                                         msg, ctypes.c_size_t(len(msg)))
+    assert rc == -3 and b"No CUDA context" in msg.value and not plan.value and skipped.value == 0
+    rc = lib.proton_em_run_cfgs(None, None, ctypes.c_int64(0), None, msg, ctypes.c_size_t(len(msg)))
+    assert rc == -3 and b"No CUDA context" in msg.value
+    rc = lib.proton_em_run_cfgs(None, None, ctypes.c_int64(3), None, msg, ctypes.c_size_t(len(msg)))
+    assert rc == -1 and b"bad arguments" in msg.value
