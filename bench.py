@@ -355,22 +355,51 @@ class Shard:
 class Gather:
     """The one exchange of the path: every rank contributes max (f64), argmax (i32) and flag (u8) of its lines at all
     timestamps, packed into one byte buffer of 13 bytes per (line, t) (padded to the longest shard), and ONE NCCL
-    all-gather moves them; queued on the library's stream right behind the evaluation."""
+    all-gather moves them.  The packing copies are queued on the library's stream right behind the evaluation; the
+    all-gather runs on a side stream from one of two send / receive buffer pairs, so the exchange of step k proceeds
+    under the evaluation of step k + 1 (the library's stream waits for it only before it reuses the pair, two steps
+    later, and in `finish()`, which the timed loops call before their closing event).  PROTON_EM_BENCH_GATHER=serial
+    keeps everything on the library's stream."""
 
     def __init__(self, torch, dist, dev, stream, Lmax, T, world):
         self.torch, self.dist, self.stream = torch, dist, stream
         self.n, self.world = Lmax * T, world
-        self.send = torch.zeros(self.n * 13, dtype=torch.uint8, device=dev)
-        self.recv = torch.empty(world * self.n * 13, dtype=torch.uint8, device=dev)
+        self.overlap = os.environ.get("PROTON_EM_BENCH_GATHER", "overlap") != "serial"
         n = self.n
-        self.views = (self.send[: 8 * n].view(torch.float64), self.send[8 * n: 12 * n].view(torch.int32), self.send[12 * n:])
+        self.bufs = []
+        for _ in range(2 if self.overlap else 1):
+            send = torch.zeros(n * 13, dtype=torch.uint8, device=dev)
+            recv = torch.empty(world * n * 13, dtype=torch.uint8, device=dev)
+            views = (send[: 8 * n].view(torch.float64), send[8 * n: 12 * n].view(torch.int32), send[12 * n:])
+            self.bufs.append((send, recv, views, torch.cuda.Event(), torch.cuda.Event()))
+        self.side = torch.cuda.Stream(device=dev) if self.overlap else None
+        self.k = 0
+        self.recv = self.bufs[0][1]
 
     def run(self, shard):
         k = shard.L * shard.T
+        send, recv, views, ready, done = self.bufs[self.k % len(self.bufs)]
+        self.k += 1
+        self.recv = recv
         with self.torch.cuda.stream(self.stream):
-            for view, src in zip(self.views, (shard.d_mx, shard.d_amx, shard.d_flag)):
+            if self.overlap:
+                self.stream.wait_event(done)          # the pair is free again (no-op until it has been used once)
+            for view, src in zip(views, (shard.d_mx, shard.d_amx, shard.d_flag)):
                 view[:k].copy_(src)
-            self.dist.all_gather_into_tensor(self.recv, self.send)
+            if not self.overlap:
+                self.dist.all_gather_into_tensor(recv, send)
+                return
+            ready.record(self.stream)
+        with self.torch.cuda.stream(self.side):
+            self.side.wait_event(ready)
+            self.dist.all_gather_into_tensor(recv, send)
+            done.record(self.side)
+        self.last_done = done
+
+    def finish(self):
+        """The library's stream waits for the exchange that is still in flight."""
+        if self.overlap and self.k:
+            self.stream.wait_event(self.last_done)
 
     def unpack(self):
         """-> [max (world*n f64), argmax (world*n i32), flag (world*n u8)] as numpy, rank-major."""
@@ -381,12 +410,14 @@ class Gather:
                 np.ascontiguousarray(raw[:, 12 * n:]).reshape(-1)]
 
 
-def time_steps(torch, stream, step, n, barrier):
+def time_steps(torch, stream, step, n, barrier, finish=None):
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     for _ in range(n):
         step()
+    if finish is not None:
+        finish()                      # (work the steps left on other streams: the closing event waits for it)
     ev1.record(stream)
     barrier()
     return ev0.elapsed_time(ev1) / n
@@ -491,7 +522,7 @@ def main():
     sampler = ClockSampler(local_rank)
     sampler.start()
     launches0 = ctx.launch_count
-    ms_rank = time_steps(torch, stream, step, args.steps, barrier)
+    ms_rank = time_steps(torch, stream, step, args.steps, barrier, gth.finish if world > 1 else None)
     launches = ctx.launch_count - launches0
     clocks = sampler.stop()
     ms = allmax(ms_rank)
@@ -502,7 +533,7 @@ def main():
     if world > 1:
         n_sub = max(3, min(args.steps, 10))
         ms_eval = time_steps(torch, stream, shard.eval, n_sub, barrier)
-        ms_gather = time_steps(torch, stream, gather, n_sub, barrier)
+        ms_gather = time_steps(torch, stream, gather, n_sub, barrier, gth.finish)
         stats = torch.tensor([ms_eval, ms_gather, float(batch.total_nodes), float(L)], device=dev, dtype=torch.float64)
         allstats = torch.empty(world * 4, device=dev, dtype=torch.float64)
         dist.all_gather_into_tensor(allstats, stats)
@@ -511,6 +542,8 @@ def main():
                  "eval_ms_min": float(a[:, 0].min()), "eval_ms_max": float(a[:, 0].max()),
                  "imbalance_of_time_max_over_mean": float(a[:, 0].max() / a[:, 0].mean()),
                  "gather_ms": float(a[:, 1].max()), "gather_bytes_per_rank": int(Lmax * T * 13 * world),
+                 "gather_mode": ("side stream, under the next step's evaluation (two buffer pairs)" if gth.overlap
+                                 else "on the library's stream, behind the evaluation"),
                  "nodes_per_rank": [int(x) for x in a[:, 2]], "lines_per_rank": [int(x) for x in a[:, 3]]}
         # rank 0 checks the gathered reductions of lines owned by OTHER ranks against the CPU oracle
         barrier()
@@ -803,9 +836,9 @@ def run_config4(args, ctx, torch, dist, dev, stream, W, world, rank, barrier, al
     n = max(5, min(args.steps, 20))
     for _ in range(3):
         step()
-    ms_step = allmax(time_steps(torch, stream, step, n, barrier))
+    ms_step = allmax(time_steps(torch, stream, step, n, barrier, gth.finish))
     ms_eval = time_steps(torch, stream, sh.eval, n, barrier)
-    ms_gather = allmax(time_steps(torch, stream, gather, n, barrier))
+    ms_gather = allmax(time_steps(torch, stream, gather, n, barrier, gth.finish))
     stats = torch.tensor([ms_eval, float(mine.total_nodes)], device=dev, dtype=torch.float64)
     allstats = torch.empty(world * 2, device=dev, dtype=torch.float64)
     dist.all_gather_into_tensor(allstats, stats)
